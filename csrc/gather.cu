@@ -1,0 +1,566 @@
+// N5 exchange_gather_collate, pull form: the hot kernel of the loader.
+//
+// One launch assembles one batch: for every slot id (source << 48 | row) of the consumer's
+// window slice it pulls the sample from the owning shard -- local HBM, an NVLink peer mapping
+// or mapped pinned host memory, all just addresses in d_src_base -- converts it
+// (uint8 -> bf16 normalise, fp32 -> bf16, ...) and writes row i of the batch tensor.  This is
+// the reference's batch extraction (ddl/mpi_dataloader.py:179-198), the data half of its
+// global shuffle (ddl/shuffle.py:92-108: rows cross the fabric once, here) and the H2D copy it
+// leaves to the user (tests/run_ddl.py:233-235), fused.
+//
+// Work item = (sample, chunk).  Every warp runs its own pipeline over a private ring of
+// shared-memory stages, so there is no inter-warp synchronisation at all:
+//   * TMA/copy   : lane 0 alone issues cp.async.bulk global->shared (mbarrier complete_tx) and
+//                  cp.async.bulk shared->global; no thread ever touches the bytes.
+//   * TMA/convert: lane 0 issues the bulk loads; the warp converts a landed stage with
+//                  LDS -> ALU -> STG.128 and re-arms the stage.
+//   * LDG        : no shared memory, ld.global.nc.v4 -> convert -> st.global.v4 (tiny rows,
+//                  and the comparison baseline for the TMA forms).
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include "../include/ddl_b200.h"
+#include "common.h"
+#include "launch_count.h"
+#include "ptx.cuh"
+
+namespace {
+
+using namespace bddl;
+
+constexpr int kWarps = 8;  // warps per CTA, each with a private stage ring
+constexpr uint64_t kRowMask = (1ULL << BDDL_SLOT_ROW_BITS) - 1;
+
+struct KParams {
+    const void* const* src_base;
+    const int64_t* const* src_offsets;
+    const int32_t* const* src_lengths;
+    const uint64_t* slots;
+    uint8_t* dst;
+    int64_t row_bytes;
+    int64_t sample_bytes;
+    int64_t dst_row_bytes;
+    uint32_t chan_stride;
+    int32_t n_channels;
+    uint32_t n_items;
+    uint32_t chunks_per_sample;
+    uint32_t pad_bits;
+    float scale[BDDL_MAX_CHANNELS];
+    float bias[BDDL_MAX_CHANNELS];
+};
+
+template <int MODE>
+struct Cvt;
+template <>
+struct Cvt<BDDL_CVT_COPY> {
+    static constexpr int IN_ES = 1, OUT_ES = 1, PER = 16;
+};
+template <>
+struct Cvt<BDDL_CVT_U8_BF16> {
+    static constexpr int IN_ES = 1, OUT_ES = 2, PER = 8;
+};
+template <>
+struct Cvt<BDDL_CVT_F32_BF16> {
+    static constexpr int IN_ES = 4, OUT_ES = 2, PER = 8;
+};
+template <>
+struct Cvt<BDDL_CVT_U8_F32> {
+    static constexpr int IN_ES = 1, OUT_ES = 4, PER = 4;
+};
+template <>
+struct Cvt<BDDL_CVT_I32_I64> {
+    static constexpr int IN_ES = 4, OUT_ES = 8, PER = 2;
+};
+
+struct Item {
+    const uint8_t* src;
+    uint8_t* dst;
+    uint32_t in_bytes;      // payload bytes of this chunk (0 = nothing to load)
+    uint32_t region_bytes;  // input-byte extent this item is responsible for (payload + padding)
+    uint32_t elem0;         // index of the chunk's first element inside the sample
+};
+
+template <int MODE, int CHUNK>
+__device__ __forceinline__ Item resolve_item(const KParams& p, uint32_t item) {
+    using C = Cvt<MODE>;
+    const uint32_t s = item / p.chunks_per_sample;
+    const uint32_t c = item - s * p.chunks_per_sample;
+    const uint64_t slot = __ldg(p.slots + s);
+    const uint32_t source = (uint32_t)(slot >> BDDL_SLOT_ROW_BITS);
+    const uint64_t row = slot & kRowMask;
+    const uint8_t* base = (const uint8_t*)__ldg((const unsigned long long*)(p.src_base + source));
+    int64_t off, len;
+    if (p.src_offsets) {
+        const int64_t* offs = (const int64_t*)__ldg((const unsigned long long*)(p.src_offsets + source));
+        const int32_t* lens = (const int32_t*)__ldg((const unsigned long long*)(p.src_lengths + source));
+        off = __ldg(offs + row);
+        len = __ldg(lens + row);
+    } else {
+        off = (int64_t)row * p.row_bytes;
+        len = p.sample_bytes;
+    }
+    const int64_t start = (int64_t)c * CHUNK;
+    Item it;
+    it.in_bytes = len > start ? (uint32_t)min((int64_t)CHUNK, len - start) : 0u;
+    it.region_bytes = (uint32_t)min((int64_t)CHUNK, p.sample_bytes - start);
+    it.src = base + off + start;
+    it.elem0 = (uint32_t)(start / C::IN_ES);
+    it.dst = p.dst + (int64_t)s * p.dst_row_bytes + (int64_t)it.elem0 * C::OUT_ES;
+    return it;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// x*scale + bias with two roundings, so results match a plain fp32 PyTorch expression exactly.
+__device__ __forceinline__ float affine(float x, float sc, float bi) { return __fadd_rn(__fmul_rn(x, sc), bi); }
+
+template <bool CHAN>
+__device__ __forceinline__ int channel_of(const KParams& p, uint32_t e) {
+    if (!CHAN) return 0;
+    return (int)((e / p.chan_stride) % (uint32_t)p.n_channels);
+}
+
+// Source loads: G = global memory through the read-only path, otherwise shared memory.
+template <bool G>
+__device__ __forceinline__ uint4 ld16(const uint8_t* q) {
+    if constexpr (G) return __ldg(reinterpret_cast<const uint4*>(q));
+    return *reinterpret_cast<const uint4*>(q);
+}
+template <bool G>
+__device__ __forceinline__ uint2 ld8(const uint8_t* q) {
+    if constexpr (G) return __ldg(reinterpret_cast<const uint2*>(q));
+    return *reinterpret_cast<const uint2*>(q);
+}
+template <bool G>
+__device__ __forceinline__ uint32_t ld4(const uint8_t* q) {
+    if constexpr (G) return __ldg(reinterpret_cast<const uint32_t*>(q));
+    return *reinterpret_cast<const uint32_t*>(q);
+}
+template <bool G>
+__device__ __forceinline__ uint8_t ld1(const uint8_t* q) {
+    if constexpr (G) return __ldg(q);
+    return *q;
+}
+
+// One output vector (16 bytes) from PER input elements starting at src.
+template <int MODE, bool CHAN, bool G>
+__device__ __forceinline__ uint4 convert_group(const KParams& p, const uint8_t* src, uint32_t e0) {
+    using C = Cvt<MODE>;
+    uint4 out;
+    if constexpr (MODE == BDDL_CVT_COPY) {
+        out = ld16<G>(src);
+    } else if constexpr (MODE == BDDL_CVT_I32_I64) {
+        const uint2 v = ld8<G>(src);
+        const long long a = (int)v.x, b = (int)v.y;
+        out.x = (uint32_t)a;
+        out.y = (uint32_t)((unsigned long long)a >> 32);
+        out.z = (uint32_t)b;
+        out.w = (uint32_t)((unsigned long long)b >> 32);
+    } else {
+        float f[C::PER];
+        if constexpr (C::IN_ES == 1) {
+            if constexpr (C::PER == 8) {
+                const uint2 v = ld8<G>(src);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    f[k] = (float)((v.x >> (8 * k)) & 0xffu);
+                    f[4 + k] = (float)((v.y >> (8 * k)) & 0xffu);
+                }
+            } else {
+                const uint32_t v = ld4<G>(src);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) f[k] = (float)((v >> (8 * k)) & 0xffu);
+            }
+        } else {
+            const uint4 a = ld16<G>(src);
+            const uint4 b = ld16<G>(src + 16);
+            f[0] = __uint_as_float(a.x), f[1] = __uint_as_float(a.y);
+            f[2] = __uint_as_float(a.z), f[3] = __uint_as_float(a.w);
+            f[4] = __uint_as_float(b.x), f[5] = __uint_as_float(b.y);
+            f[6] = __uint_as_float(b.z), f[7] = __uint_as_float(b.w);
+        }
+        const int c0 = channel_of<CHAN>(p, e0);
+        const int c1 = channel_of<CHAN>(p, e0 + C::PER - 1);
+        if (c0 == c1) {
+            const float sc = p.scale[c0], bi = p.bias[c0];
+#pragma unroll
+            for (int k = 0; k < C::PER; ++k) f[k] = affine(f[k], sc, bi);
+        } else {
+#pragma unroll
+            for (int k = 0; k < C::PER; ++k) {
+                const int c = channel_of<CHAN>(p, e0 + k);
+                f[k] = affine(f[k], p.scale[c], p.bias[c]);
+            }
+        }
+        if constexpr (C::OUT_ES == 2) {
+            out.x = pack_bf16(f[0], f[1]);
+            out.y = pack_bf16(f[2], f[3]);
+            out.z = pack_bf16(f[4], f[5]);
+            out.w = pack_bf16(f[6], f[7]);
+        } else {
+            out.x = __float_as_uint(f[0]);
+            out.y = __float_as_uint(f[1]);
+            out.z = __float_as_uint(f[2]);
+            out.w = __float_as_uint(f[3]);
+        }
+    }
+    return out;
+}
+
+// One element, for the ragged tail of a chunk.
+template <int MODE, bool CHAN, bool G>
+__device__ __forceinline__ void convert_one(const KParams& p, const uint8_t* src, uint8_t* dst, uint32_t e) {
+    if constexpr (MODE == BDDL_CVT_COPY) {
+        *dst = ld1<G>(src);
+    } else if constexpr (MODE == BDDL_CVT_I32_I64) {
+        *reinterpret_cast<long long*>(dst) = (long long)(int)ld4<G>(src);
+    } else {
+        float x;
+        if constexpr (Cvt<MODE>::IN_ES == 1)
+            x = (float)ld1<G>(src);
+        else
+            x = __uint_as_float(ld4<G>(src));
+        const int c = channel_of<CHAN>(p, e);
+        x = affine(x, p.scale[c], p.bias[c]);
+        if constexpr (Cvt<MODE>::OUT_ES == 2)
+            *reinterpret_cast<__nv_bfloat16*>(dst) = __float2bfloat16_rn(x);
+        else
+            *reinterpret_cast<float*>(dst) = x;
+    }
+}
+
+// Convert the payload of one chunk (src: shared or global) and pad the rest of its region.
+template <int MODE, bool CHAN, bool G, int UNROLL>
+__device__ __forceinline__ void convert_chunk(const KParams& p, const uint8_t* __restrict__ src,
+                                              const Item& it, int lane) {
+    using C = Cvt<MODE>;
+    uint8_t* __restrict__ dst = it.dst;
+    const uint32_t n_elems = it.in_bytes / C::IN_ES;
+    const uint32_t n_groups = n_elems / C::PER;
+#pragma unroll UNROLL
+    for (uint32_t g = lane; g < n_groups; g += 32) {
+        const uint4 v = convert_group<MODE, CHAN, G>(p, src + (size_t)g * (C::PER * C::IN_ES), it.elem0 + g * C::PER);
+        *reinterpret_cast<uint4*>(dst + (size_t)g * 16) = v;
+    }
+    const uint32_t done = n_groups * C::PER;
+    for (uint32_t e = done + lane; e < n_elems; e += 32)
+        convert_one<MODE, CHAN, G>(p, src + (size_t)e * C::IN_ES, dst + (size_t)e * C::OUT_ES, it.elem0 + e);
+    // Variable-size samples: fill [payload, region) of the batch row with the pad element.
+    const uint32_t region_elems = it.region_bytes / C::IN_ES;
+    for (uint32_t e = n_elems + lane; e < region_elems; e += 32) {
+        uint8_t* d = dst + (size_t)e * C::OUT_ES;
+        if constexpr (C::OUT_ES == 1)
+            *d = (uint8_t)p.pad_bits;
+        else if constexpr (C::OUT_ES == 2)
+            *reinterpret_cast<uint16_t*>(d) = (uint16_t)p.pad_bits;
+        else if constexpr (C::OUT_ES == 4)
+            *reinterpret_cast<uint32_t*>(d) = p.pad_bits;
+        else
+            *reinterpret_cast<long long*>(d) = (long long)(int32_t)p.pad_bits;
+    }
+}
+
+// ---- LDG form --------------------------------------------------------------------------------
+template <int MODE, bool CHAN, int CHUNK>
+__global__ void __launch_bounds__(kWarps * 32) gather_ldg_kernel(const __grid_constant__ KParams p) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t gw = blockIdx.x * kWarps + (threadIdx.x >> 5);
+    const uint32_t nw = gridDim.x * kWarps;
+    for (uint32_t item = gw; item < p.n_items; item += nw) {
+        const Item it = resolve_item<MODE, CHUNK>(p, item);
+        convert_chunk<MODE, CHAN, true, 4>(p, it.src, it, lane);
+    }
+}
+
+// ---- TMA / convert form ------------------------------------------------------------------------
+template <int MODE, bool CHAN, int CHUNK, int STAGES>
+__global__ void __launch_bounds__(kWarps * 32) gather_tma_cvt_kernel(const __grid_constant__ KParams p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    uint8_t* ring = smem + (size_t)warp * STAGES * CHUNK;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)kWarps * STAGES * CHUNK) + warp * STAGES;
+
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(full + s, 1);
+        fence_mbar_init();
+    }
+    __syncwarp();
+
+    const uint32_t gw = blockIdx.x * kWarps + warp;
+    const uint32_t nw = gridDim.x * kWarps;
+    const uint32_t n_my = gw < p.n_items ? (p.n_items - gw + nw - 1) / nw : 0;
+
+    auto issue = [&](uint32_t k) {
+        const Item it = resolve_item<MODE, CHUNK>(p, gw + k * nw);
+        if (it.in_bytes == 0) return;
+        const int s = k % STAGES;
+        const uint32_t bytes = (it.in_bytes + 15u) & ~15u;
+        mbar_arrive_expect_tx(full + s, bytes);
+        bulk_g2s(ring + (size_t)s * CHUNK, it.src, bytes, full + s);
+    };
+
+    if (lane == 0)
+        for (uint32_t k = 0; k < min(n_my, (uint32_t)STAGES); ++k) issue(k);
+
+    uint32_t phase = 0;  // one parity bit per stage
+    for (uint32_t k = 0; k < n_my; ++k) {
+        const int s = k % STAGES;
+        const Item it = resolve_item<MODE, CHUNK>(p, gw + k * nw);
+        if (it.in_bytes != 0) {
+            mbar_wait(full + s, (phase >> s) & 1u);
+            phase ^= 1u << s;
+        }
+        convert_chunk<MODE, CHAN, false, 2>(p, ring + (size_t)s * CHUNK, it, lane);
+        __syncwarp();
+        if (lane == 0 && k + STAGES < n_my) {
+            fence_proxy_async_smem();  // the warp's reads of this stage precede the next bulk write
+            issue(k + STAGES);
+        }
+    }
+}
+
+// ---- TMA / copy form ---------------------------------------------------------------------------
+// Fixed-size rows, bytes unchanged: one thread per warp moves everything with bulk copies.
+template <int CHUNK, int STAGES>
+__global__ void __launch_bounds__(kWarps * 32) gather_tma_copy_kernel(const __grid_constant__ KParams p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    if (lane != 0) return;
+    uint8_t* ring = smem + (size_t)warp * STAGES * CHUNK;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)kWarps * STAGES * CHUNK) + warp * STAGES;
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) mbar_init(full + s, 1);
+    fence_mbar_init();
+
+    const uint32_t gw = blockIdx.x * kWarps + warp;
+    const uint32_t nw = gridDim.x * kWarps;
+    const uint32_t n_my = gw < p.n_items ? (p.n_items - gw + nw - 1) / nw : 0;
+    constexpr int LAG = 2;  // bulk stores allowed to still be reading their stage
+    static_assert(STAGES > LAG, "ring too shallow");
+
+    auto issue = [&](uint32_t k) {
+        const Item it = resolve_item<BDDL_CVT_COPY, CHUNK>(p, gw + k * nw);
+        const int s = k % STAGES;
+        const uint32_t bytes = (it.in_bytes + 15u) & ~15u;
+        mbar_arrive_expect_tx(full + s, bytes);
+        bulk_g2s(ring + (size_t)s * CHUNK, it.src, bytes, full + s);
+    };
+
+    for (uint32_t k = 0; k < min(n_my, (uint32_t)STAGES); ++k) issue(k);
+    for (uint32_t k = 0; k < n_my; ++k) {
+        const int s = k % STAGES;
+        const Item it = resolve_item<BDDL_CVT_COPY, CHUNK>(p, gw + k * nw);
+        mbar_wait(full + s, (k / STAGES) & 1u);
+        bulk_s2g(it.dst, ring + (size_t)s * CHUNK, (it.in_bytes + 15u) & ~15u);
+        bulk_commit();
+        bulk_wait_read<LAG>();  // store k-LAG has drained its stage
+        if (k >= (uint32_t)LAG && k - LAG + STAGES < n_my) issue(k - LAG + STAGES);
+    }
+    bulk_wait<0>();
+}
+
+int g_sm_count[64];
+
+int sm_count(int* out) {
+    int dev = 0;
+    BDDL_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return bddl_fail(BDDL_ERR_INVALID, "device index %d out of range", dev);
+    if (g_sm_count[dev] == 0) BDDL_CUDA(cudaDeviceGetAttribute(&g_sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
+    *out = g_sm_count[dev];
+    return 0;
+}
+
+template <typename K>
+int set_smem(K kernel, size_t bytes) {
+    BDDL_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return 0;
+}
+
+template <int CHUNK>
+uint32_t chunks_for(int64_t sample_bytes) {
+    return (uint32_t)((sample_bytes + CHUNK - 1) / CHUNK);
+}
+
+int grid_for(const bddl_gather_desc* d, uint32_t n_items, int* grid) {
+    int sms = 0;
+    int rc = sm_count(&sms);
+    if (rc) return rc;
+    int cap = d->max_ctas > 0 ? d->max_ctas : sms;
+    int need = (int)((n_items + kWarps - 1) / kWarps);
+    *grid = need < cap ? need : cap;
+    if (*grid < 1) *grid = 1;
+    return 0;
+}
+
+template <int MODE, bool CHAN>
+int launch_ldg(const bddl_gather_desc* d, KParams& p, cudaStream_t st) {
+    constexpr int CHUNK = 4096;
+    p.chunks_per_sample = chunks_for<CHUNK>(d->sample_bytes);
+    p.n_items = (uint32_t)d->n_samples * p.chunks_per_sample;
+    int grid = 0;
+    // The LDG form hides latency with occupancy: allow several CTAs per SM.
+    bddl_gather_desc dd = *d;
+    if (dd.max_ctas == 0) {
+        int sms = 0;
+        int rc = sm_count(&sms);
+        if (rc) return rc;
+        dd.max_ctas = sms * 4;
+    }
+    int rc = grid_for(&dd, p.n_items, &grid);
+    if (rc) return rc;
+    gather_ldg_kernel<MODE, CHAN, CHUNK><<<grid, kWarps * 32, 0, st>>>(p);
+    bddl_count_launch(1);
+    BDDL_CUDA(cudaGetLastError());
+    return 0;
+}
+
+template <int MODE, bool CHAN, int CHUNK, int STAGES>
+int launch_tma_cvt(const bddl_gather_desc* d, KParams& p, cudaStream_t st) {
+    constexpr size_t smem = (size_t)kWarps * STAGES * CHUNK + (size_t)kWarps * STAGES * sizeof(uint64_t);
+    static bool configured[64];
+    int dev = 0;
+    BDDL_CUDA(cudaGetDevice(&dev));
+    auto kernel = gather_tma_cvt_kernel<MODE, CHAN, CHUNK, STAGES>;
+    if (!configured[dev & 63]) {
+        int rc = set_smem(kernel, smem);
+        if (rc) return rc;
+        configured[dev & 63] = true;
+    }
+    p.chunks_per_sample = chunks_for<CHUNK>(d->sample_bytes);
+    p.n_items = (uint32_t)d->n_samples * p.chunks_per_sample;
+    int grid = 0;
+    int rc = grid_for(d, p.n_items, &grid);
+    if (rc) return rc;
+    kernel<<<grid, kWarps * 32, smem, st>>>(p);
+    bddl_count_launch(1);
+    BDDL_CUDA(cudaGetLastError());
+    return 0;
+}
+
+template <int CHUNK, int STAGES>
+int launch_tma_copy(const bddl_gather_desc* d, KParams& p, cudaStream_t st) {
+    constexpr size_t smem = (size_t)kWarps * STAGES * CHUNK + (size_t)kWarps * STAGES * sizeof(uint64_t);
+    static bool configured[64];
+    int dev = 0;
+    BDDL_CUDA(cudaGetDevice(&dev));
+    auto kernel = gather_tma_copy_kernel<CHUNK, STAGES>;
+    if (!configured[dev & 63]) {
+        int rc = set_smem(kernel, smem);
+        if (rc) return rc;
+        configured[dev & 63] = true;
+    }
+    p.chunks_per_sample = chunks_for<CHUNK>(d->sample_bytes);
+    p.n_items = (uint32_t)d->n_samples * p.chunks_per_sample;
+    int grid = 0;
+    int rc = grid_for(d, p.n_items, &grid);
+    if (rc) return rc;
+    kernel<<<grid, kWarps * 32, smem, st>>>(p);
+    bddl_count_launch(1);
+    BDDL_CUDA(cudaGetLastError());
+    return 0;
+}
+
+template <int MODE, bool CHAN>
+int launch_mode(const bddl_gather_desc* d, KParams& p, bool tma, cudaStream_t st) {
+    if (!tma) return launch_ldg<MODE, CHAN>(d, p, st);
+    switch (d->tune) {
+        case 1:
+            return launch_tma_cvt<MODE, CHAN, 4096, 6>(d, p, st);
+        case 2:
+            return launch_tma_cvt<MODE, CHAN, 2048, 12>(d, p, st);
+        default:
+            return launch_tma_cvt<MODE, CHAN, 8192, 3>(d, p, st);
+    }
+}
+
+}  // namespace
+
+static int64_t g_launches = 0;
+void bddl_count_launch(int64_t n) { __atomic_fetch_add(&g_launches, n, __ATOMIC_RELAXED); }
+extern "C" int64_t bddl_launch_count(void) { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
+
+extern "C" int bddl_exchange_gather_collate(const bddl_gather_desc* d, void* stream) {
+    if (!d) return bddl_fail(BDDL_ERR_INVALID, "gather: null descriptor");
+    if (d->n_samples == 0) return 0;
+    if (!d->d_src_base || !d->d_slots || !d->d_dst || d->n_samples < 0 || d->n_sources < 1)
+        return bddl_fail(BDDL_ERR_INVALID, "gather: null pointer or bad counts");
+    if (d->mode < BDDL_CVT_COPY || d->mode > BDDL_CVT_I32_I64)
+        return bddl_fail(BDDL_ERR_INVALID, "gather: unknown conversion mode %d", d->mode);
+    if (d->sample_bytes <= 0 || d->sample_bytes >= (1LL << 31))
+        return bddl_fail(BDDL_ERR_INVALID, "gather: sample_bytes %lld out of range", (long long)d->sample_bytes);
+    if ((d->dst_row_bytes & 15) || ((uintptr_t)d->d_dst & 15))
+        return bddl_fail(BDDL_ERR_INVALID, "gather: batch rows must be 16-byte aligned (stride %lld)",
+                         (long long)d->dst_row_bytes);
+    const bool var = d->d_src_offsets != nullptr;
+    if (var && !d->d_src_lengths) return bddl_fail(BDDL_ERR_INVALID, "gather: offsets without lengths");
+    if (!var && ((d->row_bytes & 15) || d->row_bytes < d->sample_bytes))
+        return bddl_fail(BDDL_ERR_INVALID, "gather: shard row stride %lld must be a multiple of 16 and >= %lld",
+                         (long long)d->row_bytes, (long long)d->sample_bytes);
+    static const int in_es[] = {1, 1, 4, 1, 4}, out_es[] = {1, 2, 2, 4, 8};
+    if (d->sample_bytes % in_es[d->mode])
+        return bddl_fail(BDDL_ERR_INVALID, "gather: sample_bytes not a multiple of the element size");
+    const int64_t out_bytes = d->sample_bytes / in_es[d->mode] * out_es[d->mode];
+    if (d->dst_row_bytes < ((out_bytes + 15) & ~15LL))
+        return bddl_fail(BDDL_ERR_INVALID, "gather: dst_row_bytes %lld too small for %lld output bytes",
+                         (long long)d->dst_row_bytes, (long long)out_bytes);
+    const bool chan = d->n_channels > 1 && d->chan_stride > 0;
+    if (d->n_channels > BDDL_MAX_CHANNELS) return bddl_fail(BDDL_ERR_INVALID, "gather: too many channels");
+
+    KParams p;
+    p.src_base = d->d_src_base;
+    p.src_offsets = d->d_src_offsets;
+    p.src_lengths = d->d_src_lengths;
+    p.slots = d->d_slots;
+    p.dst = (uint8_t*)d->d_dst;
+    p.row_bytes = d->row_bytes;
+    p.sample_bytes = d->sample_bytes;
+    p.dst_row_bytes = d->dst_row_bytes;
+    p.chan_stride = chan ? (uint32_t)d->chan_stride : 1u;
+    p.n_channels = chan ? d->n_channels : 1;
+    p.pad_bits = d->pad_bits;
+    for (int i = 0; i < BDDL_MAX_CHANNELS; ++i) {
+        p.scale[i] = d->scale[i];
+        p.bias[i] = d->bias[i];
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+
+    bool tma;
+    if (d->variant == BDDL_VARIANT_LDG)
+        tma = false;
+    else if (d->variant == BDDL_VARIANT_TMA)
+        tma = true;
+    else
+        tma = d->sample_bytes >= 2048;
+
+    switch (d->mode) {
+        case BDDL_CVT_COPY:
+            if (tma && !var) {
+                switch (d->tune) {
+                    case 1:
+                        return launch_tma_copy<4096, 6>(d, p, st);
+                    case 2:
+                        return launch_tma_copy<2048, 12>(d, p, st);
+                    default:
+                        return launch_tma_copy<8192, 3>(d, p, st);
+                }
+            }
+            return launch_mode<BDDL_CVT_COPY, false>(d, p, tma, st);
+        case BDDL_CVT_U8_BF16:
+            return chan ? launch_mode<BDDL_CVT_U8_BF16, true>(d, p, tma, st)
+                        : launch_mode<BDDL_CVT_U8_BF16, false>(d, p, tma, st);
+        case BDDL_CVT_F32_BF16:
+            return chan ? launch_mode<BDDL_CVT_F32_BF16, true>(d, p, tma, st)
+                        : launch_mode<BDDL_CVT_F32_BF16, false>(d, p, tma, st);
+        case BDDL_CVT_U8_F32:
+            return chan ? launch_mode<BDDL_CVT_U8_F32, true>(d, p, tma, st)
+                        : launch_mode<BDDL_CVT_U8_F32, false>(d, p, tma, st);
+        default:
+            return launch_mode<BDDL_CVT_I32_I64, false>(d, p, tma, st);
+    }
+}

@@ -1,0 +1,165 @@
+// N7 heap + N9 stage_host: device memory that peers can map, pinned host staging, and the
+// small set of CUDA runtime calls the Python runtime needs without going through torch.
+//
+// The reference keeps every producer's data in an MPI-3 shared-memory window that all ranks of
+// an instance map (Win.Allocate_shared / Shared_query, reference ddl/connection.py:88-139).
+// The B200 equivalent is a symmetric heap in HBM: each process cudaMallocs its segment, exports
+// a CUDA IPC handle, and every peer maps it, after which kernels address remote shards with
+// plain pointers over NVLink.  Host-resident datasets live in pinned, device-mapped memory and
+// are either pulled by the kernel directly or staged with one cudaMemcpyAsync per contiguous
+// run on a side stream (the reference's window fill, tests/run_ddl.py:152-161).
+#include <cuda_runtime.h>
+#include <string.h>
+
+#include "../include/ddl_b200.h"
+#include "common.h"
+#include "launch_count.h"
+
+extern "C" {
+
+int bddl_device_count(int32_t* n) {
+    int c = 0;
+    cudaError_t e = cudaGetDeviceCount(&c);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        c = 0;
+    }
+    *n = c;
+    return 0;
+}
+
+int bddl_set_device(int32_t dev) {
+    BDDL_CUDA(cudaSetDevice(dev));
+    return 0;
+}
+
+int bddl_get_device(int32_t* dev) {
+    int d = 0;
+    BDDL_CUDA(cudaGetDevice(&d));
+    *dev = d;
+    return 0;
+}
+
+int bddl_malloc(void** p, size_t bytes) {
+    if (!p) return bddl_fail(BDDL_ERR_INVALID, "malloc: null out pointer");
+    BDDL_CUDA(cudaMalloc(p, bytes ? bytes : 16));
+    return 0;
+}
+
+int bddl_free(void* p) {
+    if (p) BDDL_CUDA(cudaFree(p));
+    return 0;
+}
+
+int bddl_memset_async(void* p, int value, size_t bytes, void* stream) {
+    BDDL_CUDA(cudaMemsetAsync(p, value, bytes, (cudaStream_t)stream));
+    return 0;
+}
+
+int bddl_memcpy_async(void* dst, const void* src, size_t bytes, int32_t kind, void* stream) {
+    // kind: 1 = host->device, 2 = device->host, 3 = device->device, 4 = default (UVA)
+    cudaMemcpyKind k = kind == 1   ? cudaMemcpyHostToDevice
+                       : kind == 2 ? cudaMemcpyDeviceToHost
+                       : kind == 3 ? cudaMemcpyDeviceToDevice
+                                   : cudaMemcpyDefault;
+    BDDL_CUDA(cudaMemcpyAsync(dst, src, bytes, k, (cudaStream_t)stream));
+    return 0;
+}
+
+int bddl_stream_synchronize(void* stream) {
+    BDDL_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return 0;
+}
+
+int bddl_ipc_get_handle(void* p, uint8_t handle[64]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    BDDL_CUDA(cudaIpcGetMemHandle(&h, p));
+    memcpy(handle, &h, 64);
+    return 0;
+}
+
+int bddl_ipc_open_handle(const uint8_t handle[64], void** p) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    BDDL_CUDA(cudaIpcOpenMemHandle(p, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+
+int bddl_ipc_close_handle(void* p) {
+    if (p) BDDL_CUDA(cudaIpcCloseMemHandle(p));
+    return 0;
+}
+
+int bddl_can_access_peer(int32_t dev, int32_t peer, int32_t* ok) {
+    int v = 0;
+    BDDL_CUDA(cudaDeviceCanAccessPeer(&v, dev, peer));
+    *ok = v;
+    return 0;
+}
+
+int bddl_enable_peer_access(int32_t peer) {
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) {
+        cudaGetLastError();
+        return 0;
+    }
+    BDDL_CUDA(e);
+    return 0;
+}
+
+// Pinned host memory, mapped into the device address space; *dev_ptr is the address kernels use.
+int bddl_host_alloc(void** host_ptr, void** dev_ptr, size_t bytes) {
+    if (!host_ptr) return bddl_fail(BDDL_ERR_INVALID, "host_alloc: null out pointer");
+    BDDL_CUDA(cudaHostAlloc(host_ptr, bytes ? bytes : 16, cudaHostAllocMapped | cudaHostAllocPortable));
+    if (dev_ptr) BDDL_CUDA(cudaHostGetDevicePointer(dev_ptr, *host_ptr, 0));
+    return 0;
+}
+
+int bddl_host_free(void* host_ptr) {
+    if (host_ptr) BDDL_CUDA(cudaFreeHost(host_ptr));
+    return 0;
+}
+
+// Pin and map memory that already exists (a POSIX shared-memory window, a numpy array).
+int bddl_host_register(void* host_ptr, size_t bytes, void** dev_ptr) {
+    BDDL_CUDA(cudaHostRegister(host_ptr, bytes, cudaHostRegisterMapped | cudaHostRegisterPortable));
+    if (dev_ptr) BDDL_CUDA(cudaHostGetDevicePointer(dev_ptr, host_ptr, 0));
+    return 0;
+}
+
+int bddl_host_unregister(void* host_ptr) {
+    if (host_ptr) BDDL_CUDA(cudaHostUnregister(host_ptr));
+    return 0;
+}
+
+// N9 stage_host: copy n_rows rows (indices rows[], stride row_bytes in the pinned source) into
+// consecutive rows of a device staging buffer, merging runs of adjacent source rows into one
+// cudaMemcpyAsync each.  Returns the number of copies issued through *n_copies.
+int bddl_stage_rows(void* d_dst, int64_t dst_row_bytes, const void* h_src, int64_t row_bytes,
+                    const int64_t* rows, int64_t n_rows, int64_t copy_bytes, void* stream, int64_t* n_copies) {
+    if (!d_dst || !h_src || (!rows && n_rows > 0) || copy_bytes > row_bytes || copy_bytes > dst_row_bytes)
+        return bddl_fail(BDDL_ERR_INVALID, "stage_rows: bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    int64_t copies = 0;
+    const bool dense = copy_bytes == row_bytes && row_bytes == dst_row_bytes;
+    int64_t i = 0;
+    while (i < n_rows) {
+        int64_t j = i + 1;
+        if (dense)
+            while (j < n_rows && rows[j] == rows[j - 1] + 1) ++j;
+        if (dense) {
+            BDDL_CUDA(cudaMemcpyAsync((char*)d_dst + i * dst_row_bytes, (const char*)h_src + rows[i] * row_bytes,
+                                      (size_t)((j - i) * row_bytes), cudaMemcpyHostToDevice, st));
+        } else {
+            BDDL_CUDA(cudaMemcpyAsync((char*)d_dst + i * dst_row_bytes, (const char*)h_src + rows[i] * row_bytes,
+                                      (size_t)copy_bytes, cudaMemcpyHostToDevice, st));
+        }
+        ++copies;
+        i = j;
+    }
+    if (n_copies) *n_copies = copies;
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,166 @@
+// N2 perm_gen: bit-exact numpy Generator.shuffle on slot tables, on the GPU.
+//
+// Replaces the reference's per-iteration in-place row shuffle (user execute_function:
+// rng.shuffle(my_ary), reference tests/run_ddl.py:163-167, driven from ddl/datapusher.py:154).
+// Rows never move here: the permutation is applied to a table of 64-bit slot ids.
+//
+// Fisher-Yates with masked rejection is a sequential chain, so the design
+// is one warp per table that walks the 32-bit draw stream 32 draws at a time:
+//   * each lane owns one draw of the batch (PCG64 is an LCG: lane l keeps its own state and
+//     jumps 16 outputs per batch, so the raw stream is produced in parallel);
+//   * accept/reject of all 32 draws is resolved with one ballot when no draw lands in the
+//     32-wide ambiguous band under the running index (probability ~1024/i per batch);
+//   * the accepted swaps of a batch touch disjoint entries unless two draws collide
+//     (__match_any_sync), so they are applied as 32 parallel swaps;
+//   * any batch that is ambiguous, collides, crosses a power-of-two mask boundary or reaches
+//     the end of the table replays its 32 draws one at a time (exact sequential semantics).
+// Table accesses go through L2 (ld/st .cg) so that lanes always see each other's swaps.
+// The kernel is latency-bound by construction and is meant to run one iteration ahead on a
+// side stream, off the batch-delivery critical path.
+#include <cuda_runtime.h>
+
+#include "../include/ddl_b200.h"
+#include "common.h"
+#include "launch_count.h"
+#include "rng_pcg64.h"
+
+namespace {
+
+__device__ __forceinline__ U128 shfl_u128(U128 v, int src) {
+    U128 r;
+    r.lo = __shfl_sync(0xffffffffu, v.lo, src);
+    r.hi = __shfl_sync(0xffffffffu, v.hi, src);
+    return r;
+}
+
+__global__ void __launch_bounds__(32) perm_gen_kernel(uint64_t* tables, int64_t table_stride, int64_t n,
+                                                      BddlRng* states) {
+    const int lane = threadIdx.x;
+    uint64_t* tbl = tables + (int64_t)blockIdx.x * table_stride;
+    BddlRng* gst = states + blockIdx.x;
+
+    // Warp-uniform copy of the generator.
+    U128 base = {gst->state_lo, gst->state_hi};
+    const U128 inc = {gst->inc_lo, gst->inc_hi};
+    uint32_t has32 = gst->has_uint32;
+    uint32_t pending = gst->uinteger;
+    uint64_t draws = gst->draws32;
+
+    int64_t i = n - 1;
+
+    // Prologue: a buffered upper half from an earlier call is the first draw of the stream.
+    while (has32 && i >= 1) {
+        uint64_t mask = bddl_mask_for((uint64_t)i);
+        uint64_t v = (uint64_t)pending & mask;
+        has32 = 0;
+        draws++;
+        if (v <= (uint64_t)i) {
+            if (lane == 0) {
+                uint64_t a = __ldcg(tbl + i), b = __ldcg(tbl + v);
+                __stcg(tbl + i, b);
+                __stcg(tbl + v, a);
+            }
+            __syncwarp();
+            --i;
+        }
+    }
+
+    if (i >= 1) {
+        // 16-output jump, and lane l positioned (l/2 + 1) outputs after `base`.
+        U128 j16m, j16p;
+        pcg_jump_coeffs(inc, 16, &j16m, &j16p);
+        U128 lm, lp;
+        pcg_jump_coeffs(inc, (uint64_t)(lane / 2 + 1), &lm, &lp);
+        U128 st = u128_add(u128_mul(lm, base), lp);
+
+        while (i >= 1) {
+            const uint64_t out = pcg_output(st);
+            const uint32_t d = (lane & 1) ? (uint32_t)(out >> 32) : (uint32_t)out;
+            const uint64_t mask = bddl_mask_for((uint64_t)i);
+            const uint64_t seg_lo = (mask >> 1) + 1;  // smallest index sharing this mask
+            // Fast path needs every index of the batch (i .. i-31) to share one mask.
+            bool fast = (uint64_t)i >= seg_lo + 32;
+            const uint64_t v = (uint64_t)d & mask;
+            // v <= i-32 is accepted whatever index the lane ends up with, and then lies
+            // strictly below every index of the batch; v > i is rejected; in between the
+            // outcome depends on the accepts of earlier lanes.
+            const bool accept = v + 32 <= (uint64_t)i;
+            if (fast) {
+                const bool ambiguous = !accept && v <= (uint64_t)i;
+                fast = !__any_sync(0xffffffffu, ambiguous);
+            }
+            if (fast) {
+                const unsigned acc = __ballot_sync(0xffffffffu, accept);
+                bool collide = false;
+                if (accept) collide = __match_any_sync(acc, v) != (1u << lane);
+                fast = !__any_sync(0xffffffffu, collide);
+                if (fast) {
+                    if (accept) {
+                        const int64_t my_i = i - (int64_t)__popc(acc & ((1u << lane) - 1u));
+                        const uint64_t a = __ldcg(tbl + my_i), b = __ldcg(tbl + v);
+                        __stcg(tbl + my_i, b);
+                        __stcg(tbl + v, a);
+                    }
+                    __syncwarp();
+                    i -= (int64_t)__popc(acc);
+                    draws += 32;
+                    base = shfl_u128(st, 31);  // state after 16 outputs
+                    st = u128_add(u128_mul(j16m, st), j16p);
+                    continue;
+                }
+            }
+            // Replay: consume this batch's draws in order with the exact sequential rule.
+            int used = 0;
+            for (int t = 0; t < 32 && i >= 1; ++t) {
+                const uint32_t dt = __shfl_sync(0xffffffffu, d, t);
+                const uint64_t m = bddl_mask_for((uint64_t)i);
+                const uint64_t vt = (uint64_t)dt & m;
+                used = t + 1;
+                if (vt <= (uint64_t)i) {
+                    if (lane == 0) {
+                        const uint64_t a = __ldcg(tbl + i), b = __ldcg(tbl + vt);
+                        __stcg(tbl + i, b);
+                        __stcg(tbl + vt, a);
+                    }
+                    __syncwarp();
+                    --i;
+                }
+            }
+            draws += (uint64_t)used;
+            if (used == 32) {
+                base = shfl_u128(st, 31);
+                st = u128_add(u128_mul(j16m, st), j16p);
+            } else {
+                // Table finished mid-batch: leave the generator exactly where numpy would.
+                const int outs = (used + 1) / 2;  // 64-bit outputs consumed from this batch
+                base = shfl_u128(st, 2 * (outs - 1));
+                if (used & 1) {
+                    has32 = 1;
+                    pending = __shfl_sync(0xffffffffu, d, used);  // upper half of the last output
+                }
+            }
+        }
+    }
+
+    if (lane == 0) {
+        gst->state_lo = base.lo;
+        gst->state_hi = base.hi;
+        gst->has_uint32 = has32;
+        gst->uinteger = pending;
+        gst->draws32 = draws;
+    }
+}
+
+}  // namespace
+
+extern "C" int bddl_perm_gen(uint64_t* d_tables, int64_t table_stride, int64_t n, bddl_rng_state* d_states,
+                             int32_t n_tables, void* stream) {
+    if (!d_tables || !d_states || n < 0 || n_tables < 1 || table_stride < n)
+        return bddl_fail(BDDL_ERR_INVALID, "perm_gen: bad arguments (n=%lld tables=%d stride=%lld)",
+                         (long long)n, n_tables, (long long)table_stride);
+    if (n >= (1LL << 32)) return bddl_fail(BDDL_ERR_UNSUPPORTED, "perm_gen: tables beyond 2^32 entries");
+    perm_gen_kernel<<<n_tables, 32, 0, (cudaStream_t)stream>>>(d_tables, table_stride, n, (BddlRng*)d_states);
+    bddl_count_launch(1);
+    BDDL_CUDA(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,169 @@
+"""ctypes binding of the native library (``ddl_b200/lib/libddl_b200.so``, C ABI in
+``include/ddl_b200.h``).
+
+The reference (maximilian-tech/ddl) is pure Python over mpi4py and has no native layer; this
+module is where the framework's hand-written sm_100a kernels and C++ runtime are reached from
+Python.  The library is built in-tree by ``__graft_entry__.build()`` / ``python -m
+ddl_b200.build`` and loads on machines without a GPU (the host RNG, partner selection and
+shuffles need none).  On a machine with a GPU a missing library is an error, never a silent
+fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libddl_b200.so")
+_lib: Optional[C.CDLL] = None
+
+
+class NativeError(RuntimeError):
+    """A native entry point returned a non-zero code."""
+
+    def __init__(self, code: int, message: str):
+        super().__init__(f"ddl_b200 native error {code}: {message}")
+        self.code = code
+
+
+class RngState(C.Structure):
+    """Mirror of ``bddl_rng_state``: numpy PCG64 state + the buffered 32-bit half."""
+
+    _fields_ = [
+        ("state_lo", C.c_uint64),
+        ("state_hi", C.c_uint64),
+        ("inc_lo", C.c_uint64),
+        ("inc_hi", C.c_uint64),
+        ("has_uint32", C.c_uint32),
+        ("uinteger", C.c_uint32),
+        ("draws32", C.c_uint64),
+    ]
+
+
+MAX_CHANNELS = 8
+SLOT_ROW_BITS = 48
+
+CVT_COPY, CVT_U8_BF16, CVT_F32_BF16, CVT_U8_F32, CVT_I32_I64 = range(5)
+VARIANT_AUTO, VARIANT_LDG, VARIANT_TMA = range(3)
+
+
+class GatherDesc(C.Structure):
+    """Mirror of ``bddl_gather_desc``."""
+
+    _fields_ = [
+        ("d_src_base", C.c_void_p),
+        ("d_src_offsets", C.c_void_p),
+        ("d_src_lengths", C.c_void_p),
+        ("d_slots", C.c_void_p),
+        ("d_dst", C.c_void_p),
+        ("row_bytes", C.c_int64),
+        ("sample_bytes", C.c_int64),
+        ("dst_row_bytes", C.c_int64),
+        ("chan_stride", C.c_int64),
+        ("n_samples", C.c_int32),
+        ("n_sources", C.c_int32),
+        ("mode", C.c_int32),
+        ("n_channels", C.c_int32),
+        ("scale", C.c_float * MAX_CHANNELS),
+        ("bias", C.c_float * MAX_CHANNELS),
+        ("pad_bits", C.c_uint32),
+        ("variant", C.c_int32),
+        ("max_ctas", C.c_int32),
+        ("tune", C.c_int32),
+    ]
+
+
+def lib_path() -> str:
+    return _LIB_PATH
+
+
+def available() -> bool:
+    return os.path.exists(_LIB_PATH)
+
+
+def _declare(lib: C.CDLL) -> None:
+    P = C.POINTER
+    vp, i32, i64, u32, u64 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_uint64
+    sigs = {
+        "bddl_last_error": (C.c_char_p, []),
+        "bddl_abi_version": (C.c_int, []),
+        "bddl_rng_seed": (None, [P(RngState), u64]),
+        "bddl_rng_next32": (u32, [P(RngState)]),
+        "bddl_rng_next64": (u64, [P(RngState)]),
+        "bddl_rng_interval": (u64, [P(RngState), u64]),
+        "bddl_rng_advance": (None, [P(RngState), u64]),
+        "bddl_host_shuffle_u64": (C.c_int, [P(RngState), vp, i64]),
+        "bddl_host_shuffle_i32": (C.c_int, [P(RngState), vp, i64]),
+        "bddl_host_shuffle_rows": (C.c_int, [P(RngState), vp, i64, i64]),
+        "bddl_partner_select": (C.c_int, [P(RngState), i32, i32, P(i32), P(i32), vp, P(i32)]),
+        "bddl_perm_gen": (C.c_int, [vp, i64, i64, vp, i32, vp]),
+        "bddl_exchange_gather_collate": (C.c_int, [P(GatherDesc), vp]),
+        "bddl_launch_count": (i64, []),
+    }
+    sz = C.c_size_t
+    sigs.update({
+        "bddl_index_exchange": (C.c_int, [vp, vp, vp, vp, i64, i64, vp]),
+        "bddl_slot_iota": (C.c_int, [vp, i64, i32, i64, vp]),
+        "bddl_device_count": (C.c_int, [P(i32)]),
+        "bddl_set_device": (C.c_int, [i32]),
+        "bddl_get_device": (C.c_int, [P(i32)]),
+        "bddl_malloc": (C.c_int, [P(vp), sz]),
+        "bddl_free": (C.c_int, [vp]),
+        "bddl_memset_async": (C.c_int, [vp, C.c_int, sz, vp]),
+        "bddl_memcpy_async": (C.c_int, [vp, vp, sz, i32, vp]),
+        "bddl_stream_synchronize": (C.c_int, [vp]),
+        "bddl_ipc_get_handle": (C.c_int, [vp, vp]),
+        "bddl_ipc_open_handle": (C.c_int, [vp, P(vp)]),
+        "bddl_ipc_close_handle": (C.c_int, [vp]),
+        "bddl_can_access_peer": (C.c_int, [i32, i32, P(i32)]),
+        "bddl_enable_peer_access": (C.c_int, [i32]),
+        "bddl_host_alloc": (C.c_int, [P(vp), P(vp), sz]),
+        "bddl_host_free": (C.c_int, [vp]),
+        "bddl_host_register": (C.c_int, [vp, sz, P(vp)]),
+        "bddl_host_unregister": (C.c_int, [vp]),
+        "bddl_stage_rows": (C.c_int, [vp, i64, vp, i64, vp, i64, i64, vp, P(i64)]),
+        "bddl_stream_wait_value32": (C.c_int, [vp, vp, u32]),
+        "bddl_stream_write_value32": (C.c_int, [vp, vp, u32]),
+        "bddl_flag_signal": (C.c_int, [vp, i32, u32, i32, vp]),
+        "bddl_flag_wait": (C.c_int, [vp, u32, u64, vp, vp, vp]),
+        "bddl_flag_barrier": (C.c_int, [vp, i32, i32, u32, u64, vp, vp, vp]),
+        "bddl_shm_create": (C.c_int, [C.c_char_p, sz, P(vp)]),
+        "bddl_shm_attach": (C.c_int, [C.c_char_p, sz, P(vp)]),
+        "bddl_shm_detach": (C.c_int, [vp, sz]),
+        "bddl_shm_unlink": (C.c_int, [C.c_char_p]),
+        "bddl_hflag_store": (None, [vp, u32]),
+        "bddl_hflag_load": (u32, [vp]),
+        "bddl_hflag_add": (u32, [vp, u32]),
+        "bddl_hflag_wait_geq": (C.c_int, [vp, u32, i64, vp]),
+    })
+    optional = {}
+    for name, (res, args) in sigs.items():
+        fn = getattr(lib, name)
+        fn.restype, fn.argtypes = res, args
+    for name, (res, args) in optional.items():
+        if hasattr(lib, name):
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+
+
+def lib() -> C.CDLL:
+    """Load (once) and return the native library; build it first if it is missing."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            from . import build as _build
+
+            _build.build_native(verbose=False)
+        _lib = C.CDLL(_LIB_PATH)
+        _declare(_lib)
+    return _lib
+
+
+def check(code: int) -> None:
+    if code != 0:
+        msg = lib().bddl_last_error()
+        raise NativeError(code, msg.decode("utf-8", "replace") if msg else "")
+
+
+def launch_count() -> int:
+    return int(lib().bddl_launch_count())
