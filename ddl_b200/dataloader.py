@@ -1,0 +1,366 @@
+"""Consumer role: ``DistributedDataLoader`` (reference ddl/mpi_dataloader.py:31-249).
+
+Same constructor, ``len``/``[]``/``mark`` protocol and producer rotation as the reference:
+consumer epoch ``e`` reads the window of producer ``(e mod P) + 1`` after that producer's
+iteration ``e div P``; batch ``b`` is rows ``[b*B, (b+1)*B)`` of the window as currently
+permuted; the ``nData mod B`` tail is dropped.  What differs is where a batch
+comes from:
+
+* device transport -- one ``exchange_gather_collate`` launch per batch on a fetch stream, into a
+  ring of batch buffers in HBM, prefetched one batch ahead of the training stream.  The tensors
+  handed out are views of a ring slot and stay valid until ``ring_depth - 1`` further batches
+  have been marked.
+* process transport on a GPU -- the borrowed host window is pinned (cudaHostRegister) and the
+  batch's rows are staged with one ``cudaMemcpyAsync`` (or pulled by the kernel) on the fetch
+  stream, then converted by the same kernel.
+* process transport on the CPU -- zero-copy views of the shared window, exactly the reference.
+
+Unlike the reference a single-rank world works (reference ddl/mpi_dataloader.py:173-174 sets
+``len == 0`` and then fails in ``mark``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import logging
+import time
+from abc import ABC, abstractmethod
+from typing import Any, List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import _native as N
+from .config import LoaderConfig
+from .connection import Connection
+from .datapusher import DevicePusher
+from .datasetwrapper import ProducerFunctionSkeleton
+from .engine import DeviceEngine, NullEvent, NullStream, WindowSpec
+from .ops.gather import GatherPlan, SourceTable, make_slot
+from .types import Marker, MetaData_Consumer_To_Producer, MetaData_Producer_To_Consumer
+from .utils import for_all_methods, with_logging
+from .utils.metrics import LoaderMetrics
+
+log = logging.getLogger("ddl_b200")
+
+__all__ = ["DistributedDataLoader", "ProducerFunctionSkeleton", "Marker"]
+
+
+class DistributedDataloaderABC(ABC):
+    @abstractmethod
+    def __len__(self): ...
+
+    @abstractmethod
+    def __getitem__(self, index): ...
+
+    @abstractmethod
+    def _advance_to_next_producer(self): ...
+
+    @abstractmethod
+    def _finalize(self): ...
+
+    @abstractmethod
+    def _start_access_epoch(self, target_rank: int) -> None: ...
+
+    @abstractmethod
+    def _end_access_epoch(self, target_rank: int) -> None: ...
+
+    @abstractmethod
+    def _can_continue(self): ...
+
+    @abstractmethod
+    def mark(self, mark: Marker): ...
+
+
+@for_all_methods(with_logging, exclude=["__getitem__", "__iter__", "__len__", "mark", "_on_batch_end"])
+class DistributedDataLoader(DistributedDataloaderABC):
+    def __init__(self, producer_function: ProducerFunctionSkeleton, batch_size: int, connection: Optional[Connection],
+                 n_epochs: int, fraction_exchange: float = 0.0, exchange_method: str = "sendrecv_replace",
+                 instance_idx: int = 0, n_instances: int = 1, config: Optional[LoaderConfig] = None):
+        self.epoch = 0
+        self.batch = 0
+        self.target_rank = 1
+        self.n_epochs = n_epochs
+        self.batch_size = int(batch_size)
+        self._finalized = False
+        self._lend_seq = 0
+        self._pref: Optional[Tuple[Any, int, Any]] = None
+        self._cur_slot = -1
+        self._next_slot = 0
+
+        if connection is None:  # single process, no decorator: build the one-rank world here
+            from .parallel.topology import init_env
+
+            env = init_env(1)
+            connection = Connection(env.comm_per_gpu_shm, env, config)
+        self.connection = connection
+        self.env = connection.env
+        self.cfg = config or connection.config
+        if config is not None:
+            connection.config = config
+        self.transport = connection.transport
+        self.device = torch.device(self.env.device) if self.env is not None else torch.device("cpu")
+        self.cuda = self.device.type == "cuda"
+        self.metrics = LoaderMetrics(enabled=self.cfg.metrics)
+
+        self.metadata_to_producer = MetaData_Consumer_To_Producer(
+            producer_function=producer_function, global_shuffle_fraction_exchange=fraction_exchange,
+            global_shuffle_exchange_method=exchange_method, batch_size=self.batch_size)
+        connection.send_metadata(self.metadata_to_producer, "consumer")
+
+        if self.transport == "device":
+            self._init_device()
+        else:
+            self._init_process()
+
+        self.mode = "do_not_split_along_epoch"  # the only logically correct mode (reference :149-153)
+        self._len = self.batches_per_window[0]
+        assert self._len > 0
+        self._start_access_epoch()
+        self._prefetch(0)
+
+    # -- construction: device transport -------------------------------------------------------------------
+    def _init_device(self) -> None:
+        conn, env = self.connection, self.env
+        pushers = [DevicePusher(conn, env, k + 1) for k in range(env.n_producers)]
+        self.metadata_from_producer: List[MetaData_Producer_To_Consumer] = conn.recv_metadata_as_consumer()
+        self.splits = [m.splits for m in self.metadata_from_producer]
+        self.batches_per_window = [m.batches_per_window for m in self.metadata_from_producer]
+        specs = [WindowSpec(m) for m in self.metadata_from_producer]
+        self.engine = DeviceEngine(env, self.cfg, specs, self.batch_size)
+        conn.attach(self.engine, pushers)
+        for p in pushers:
+            p.bind(self.engine)
+        eng = self.engine
+        eng.side.synchronize()
+        eng.comm.barrier()  # every shard is resident before anyone's kernel may pull from it
+        for p in pushers:
+            p.start()
+        self._consumed = [None] * eng.ring_depth
+        self._views = {}
+        self.main = eng.main
+        self.fetch = eng.fetch
+
+    # -- construction: process transport --------------------------------------------------------------------
+    def _init_process(self) -> None:
+        conn = self.connection
+        self.metadata_from_producer = conn.recv_metadata_as_consumer()
+        self.splits = [m.splits for m in self.metadata_from_producer]
+        self.batches_per_window = [m.batches_per_window for m in self.metadata_from_producer]
+        self.specs = [WindowSpec(m) for m in self.metadata_from_producer]
+        shapes = [tuple(m.shape) for m in self.metadata_from_producer]
+        dtypes = [m.dtype for m in self.metadata_from_producer]
+        self.arys = conn.init_windows(shapes, dtypes)
+        conn.lock_windows()
+        conn.Barrier()
+        self.engine = None
+        self.cuda = self.device.type == "cuda"
+        depth = self.cfg.ring_depth
+        self._consumed = [None] * depth
+        if not self.cuda:
+            self.main = self.fetch = NullStream()
+            return
+        self.main = torch.cuda.current_stream(self.device)
+        self.fetch = torch.cuda.Stream(self.device, priority=-1)
+        lib = N.lib()
+        self._win_dev = []
+        for (ptr, nbytes) in conn.wins:  # pin + map every borrowed window once
+            d = C.c_void_p()
+            N.check(lib.bddl_host_register(C.c_void_p(ptr), nbytes, C.byref(d)))
+            self._win_dev.append(int(d.value))
+        B = self.batch_size
+        stage_row = max(s.sample_bytes for s in self.specs)
+        out_row = max(s.dst_row_bytes for s in self.specs)
+        self._stage = [torch.empty(B * stage_row, dtype=torch.uint8, device=self.device) for _ in range(depth)]
+        self._out = [torch.empty((B, out_row), dtype=torch.uint8, device=self.device) for _ in range(depth)]
+        self._plans = []
+        for k, s in enumerate(self.specs):
+            kernel_ok = s.sample_bytes % 16 == 0
+            if s.convert.mode == N.CVT_COPY and not self.cfg.host_pull:
+                self._plans.append(None)  # the staged bytes are the batch
+                continue
+            if not kernel_ok:
+                raise ValueError("converting windows need rows that are a multiple of 16 bytes")
+            if self.cfg.host_pull:
+                table = SourceTable([self._win_dev[k]], self.device)
+                slots = torch.arange(s.nData, dtype=torch.int64, device=self.device)
+            else:
+                table = SourceTable([t.data_ptr() for t in self._stage], self.device)
+                slots = torch.stack([torch.arange(B, dtype=torch.int64) + make_slot(i, 0) for i in range(depth)]).to(self.device)
+            plan = GatherPlan(table, s.sample_bytes, s.sample_bytes, s.convert, dst_row_bytes=out_row,
+                              variant=self.cfg.gather_variant, max_ctas=self.cfg.gather_max_ctas,
+                              tune=self.cfg.gather_tune)
+            self._plans.append((plan, slots))
+
+    # -- reference protocol ---------------------------------------------------------------------------------
+    def __len__(self) -> int:
+        return self._len
+
+    def __iter__(self):
+        i = 0
+        while i < self._len:
+            yield self[i]
+            i += 1
+
+    def __getitem__(self, idx: int) -> Tuple[torch.Tensor, ...]:
+        if idx >= self._len:
+            raise IndexError
+        if idx < 0:
+            raise ValueError
+        k = self.target_rank - 1
+        b = idx % self.batches_per_window[k]
+        if self.transport == "process" and not self.cuda:
+            # zero-copy views of the shared window (reference ddl/mpi_dataloader.py:190-198)
+            start = self.batch_size * b
+            data = torch.from_numpy(self.arys[k][start:start + self.batch_size])
+            self.metrics.batch(self.batch_size, data.numel() * data.element_size(), 0)
+            return torch.split(data, list(self.splits[k]), dim=1)
+        key = (self._lend_seq, b)
+        pref = self._pref
+        if pref is not None and pref[0] == key:
+            slot, ev = pref[1], pref[2]
+        else:
+            slot, ev = self._launch(k, b)
+        self._pref = None
+        if self.metrics.enabled and self.metrics.timing:
+            t0 = time.perf_counter()
+            ev.synchronize()
+            self.metrics.stall(time.perf_counter() - t0)
+        self.main.wait_event(ev)
+        self._cur_slot = slot
+        if self.cfg.prefetch and b + 1 < self.batches_per_window[k]:
+            self._prefetch(b + 1)
+        return self._batch_views(k, slot)
+
+    def _prefetch(self, b: int) -> None:
+        if not self.cfg.prefetch or (self.transport == "process" and not self.cuda) or self._finalized:
+            return
+        k = self.target_rank - 1
+        slot, ev = self._launch(k, b)
+        self._pref = ((self._lend_seq, b), slot, ev)
+
+    def _launch(self, k: int, b: int):
+        """Enqueue the assembly of batch ``b`` of window ``k`` on the fetch stream."""
+        slot = self._next_slot
+        self._next_slot = (slot + 1) % len(self._consumed)
+        done = self._consumed[slot]
+        if done is not None:
+            self.fetch.wait_event(done)  # the training stream has finished with this ring slot
+        B = self.batch_size
+        if self.transport == "device":
+            eng = self.engine
+            eng.gather(k, self.connection.pushers[k].lent_buf, b * B, slot)
+            ev = eng.event()
+            if eng.cuda:
+                ev.record(eng.fetch)
+            s = eng.specs[k]
+        else:
+            s = self.specs[k]
+            lib = N.lib()
+            fs = C.c_void_p(self.fetch.cuda_stream)
+            plan = self._plans[k]
+            if self.cfg.host_pull:
+                p, slots = plan
+                p.run_ptr(slots.data_ptr() + b * B * 8, self._out[slot].data_ptr(), B, self.fetch.cuda_stream)
+            else:
+                src = self.connection.wins[k][0] + b * B * s.sample_bytes
+                N.check(lib.bddl_memcpy_async(C.c_void_p(self._stage[slot].data_ptr()), C.c_void_p(src),
+                                              B * s.sample_bytes, 1, fs))
+                if plan is not None:
+                    p, slots = plan
+                    p.run_ptr(slots[slot].data_ptr(), self._out[slot].data_ptr(), B, self.fetch.cuda_stream)
+            ev = torch.cuda.Event()
+            ev.record(self.fetch)
+        self.metrics.batch(B, B * s.sample_bytes, B * s.out_sample_bytes)
+        return slot, ev
+
+    def _batch_views(self, k: int, slot: int):
+        if self.transport == "device":
+            v = self._views.get((k, slot))
+            if v is None:
+                v = self._views[(k, slot)] = self.engine.batch_views(k, slot)
+            return v
+        s = self.specs[k]
+        if self._plans[k] is None:
+            typed = self._stage[slot][: self.batch_size * s.sample_bytes].view(s.out_dtype).view(self.batch_size, s.nValues)
+        else:
+            raw = self._out[slot]
+            typed = (raw if s.out_dtype == torch.uint8 else raw.view(s.out_dtype))[:, : s.nValues]
+        return torch.split(typed, list(s.splits), dim=1)
+
+    def _start_access_epoch(self, target_rank: int = 0) -> None:
+        self.connection.start_access_epoch(target_rank or self.target_rank)
+        self._lend_seq += 1
+
+    def _end_access_epoch(self, target_rank: int = 0) -> None:
+        self.connection.end_access_epoch(target_rank or self.target_rank)
+
+    def _can_continue(self) -> bool:
+        return self.epoch < self.n_epochs
+
+    def _advance_to_next_producer(self) -> None:
+        self.target_rank += 1
+        if self.target_rank > self.connection.n_producers:
+            self.target_rank = 1
+        self._len = self.batches_per_window[self.target_rank - 1]
+
+    def _on_batch_end(self) -> None:
+        if self._cur_slot >= 0 and not isinstance(self.main, NullStream):
+            ev = self._consumed[self._cur_slot]
+            if ev is None:
+                ev = self._consumed[self._cur_slot] = torch.cuda.Event()
+            ev.record(self.main)  # the "free" flag of this ring slot, in stream-event form
+        self.batch += 1
+        if self.batch % self.batches_per_window[self.target_rank - 1] == 0:
+            self._end_access_epoch()
+            self._advance_to_next_producer()
+            self._start_access_epoch()
+            self._prefetch(0)
+
+    def _on_epoch_end(self) -> None:
+        self.batch = 0
+        self.epoch += 1
+        self.metrics.epoch()
+        if not self._can_continue():
+            self.connection.shutdown_operation()
+            self._finalize()
+
+    def mark(self, mark: Marker) -> None:
+        if mark is Marker.END_OF_BATCH:
+            self._on_batch_end()
+        elif mark is Marker.END_OF_EPOCH:
+            self._on_epoch_end()
+        else:
+            raise ValueError(f"Unknown mark {mark}")
+
+    def _finalize(self) -> None:
+        if self._finalized:
+            return
+        self._finalized = True
+        self._pref = None
+        if self.transport == "device":
+            self._views = {}
+            self.connection.close()
+            self.engine = None
+            return
+        if self.cuda:
+            torch.cuda.synchronize(self.device)
+            for (ptr, _n) in self.connection.wins:
+                N.lib().bddl_host_unregister(C.c_void_p(ptr))
+            self._stage, self._out, self._plans = [], [], []
+        self.connection.Barrier()
+        self.connection.unlock_windows()
+        self.connection.finalize(self.arys)
+
+    def close(self) -> None:
+        """Early shutdown (the reference can only stop by running out of epochs)."""
+        if not self._finalized:
+            self.connection.shutdown_operation()
+            self._finalize()
+
+    # -- checkpoint (absent in the reference) ---------------------------------------------------
+    def state_dict(self) -> dict:
+        d = {"epoch": self.epoch, "batch": self.batch, "target_rank": self.target_rank}
+        if self.transport == "device":
+            d["producers"] = [p.state_dict() for p in self.connection.pushers]
+            d["lent"] = [self.engine.table(p.k, p.lent_buf).cpu().numpy().copy() for p in self.connection.pushers]
+        return d

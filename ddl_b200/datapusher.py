@@ -1,0 +1,305 @@
+"""Producer role (reference ddl/datapusher.py:14-170).
+
+``DataPusher`` is the reference's producer *process*: it receives the user's producer function
+from the consumer, asks it about its data (``on_init``), creates its shared window, lets the
+user fill it (``post_init``) and then loops ``global_shuffle -> execute_function -> offer ->
+(consumer reads) -> take back`` until shutdown.
+
+``DevicePusher`` is the same state machine as a role inside the consumer process of the device
+transport: "producing" means enqueueing ``index_exchange`` + ``perm_gen`` on the engine's side
+stream, "offering" means recording a CUDA event, and nothing ever blocks the host.
+"""
+from __future__ import annotations
+
+import logging
+import pickle
+from abc import ABC, abstractmethod
+from typing import Any, List, Optional
+
+import numpy as np
+
+from .connection import Connection
+from .ops.rng import Pcg64
+from .shuffle import DeviceGlobalShuffler, make_global_shuffler
+from .types import (DataProducerOnInitReturn, MetaData_Consumer_To_Producer, MetaData_Producer_To_Consumer,
+                    WorkerInfo)
+from .utils import execute_callbacks, for_all_methods, with_logging
+
+log = logging.getLogger("ddl_b200")
+
+__all__ = ["DataPusher", "DevicePusher", "DataProducerOnInitReturn"]
+
+
+def _meta_from_init(ret: DataProducerOnInitReturn, batch_size: int) -> MetaData_Producer_To_Consumer:
+    bpw = ret.nData // batch_size
+    assert bpw > 0, "a window must hold at least one batch"
+    return MetaData_Producer_To_Consumer(
+        nData=ret.nData, nValues=ret.nValues, shape=tuple(ret.shape), splits=tuple(ret.splits),
+        batches_per_window=bpw, dtype=getattr(ret, "dtype", np.float32), convert=getattr(ret, "convert", None),
+        shuffle_seed=getattr(ret, "shuffle_seed", None))
+
+
+class DataPusherABC(ABC):
+    @abstractmethod
+    def push_data(self) -> None: ...
+
+    @abstractmethod
+    def sync(self) -> None: ...
+
+    @abstractmethod
+    def _finalize(self) -> None: ...
+
+
+@for_all_methods(with_logging)
+class DataPusher(DataPusherABC):
+    """Producer process of the ``process`` transport (reference ddl/datapusher.py:44-170)."""
+
+    def __init__(self, connection: Connection, comm_per_gpu_shm, comm_nth_pusher, comm_global) -> None:
+        self.callbacks: List[Any] = []
+        self.connection = connection
+        self.compat = connection.config.compat == "as_wired"
+        self.comm_per_gpu_shm = comm_per_gpu_shm
+        self.rank_per_gpu_shm: int = comm_per_gpu_shm.Get_rank()
+        self.rank_global: int = comm_global.Get_rank()
+        self.n_instance: int = comm_nth_pusher.Get_size()
+        self.iterations = 0
+
+        self.metadata_from_consumer: MetaData_Consumer_To_Producer = connection.recv_metadata_as_producer()
+        self.callbacks.append(self.metadata_from_consumer.producer_function)
+        on_init_return: DataProducerOnInitReturn = execute_callbacks(
+            "on_init", callbacks=self.callbacks, compat=self.compat, rank_global=self.rank_global)
+        self.metadata_to_consumer = _meta_from_init(on_init_return, self.metadata_from_consumer.batch_size)
+        connection.send_metadata(self.metadata_to_consumer, "producer")
+
+        self.arys = connection.init_windows(shapes=self.metadata_to_consumer.shape,
+                                            dtypes=self.metadata_to_consumer.dtype)
+        self.my_ary = self.arys[self.rank_per_gpu_shm - 1]  # rank 0 is the consumer and owns no window
+        connection.lock_windows()
+
+        num_exchange = int(on_init_return.nData * self.metadata_from_consumer.global_shuffle_fraction_exchange)
+        self.global_shuffler = None
+        if self.n_instance > 1 and num_exchange > 0:
+            self.global_shuffler = make_global_shuffler(
+                self.metadata_from_consumer.global_shuffle_exchange_method, self.my_ary, num_exchange,
+                comm_nth_pusher, comm_global)
+            self.callbacks.append(self.global_shuffler)
+
+        connection.sync(self.rank_per_gpu_shm)
+        execute_callbacks("post_init", callbacks=self.callbacks, compat=self.compat, rank_global=self.rank_global,
+                          my_ary=self.my_ary, n_instance=self.n_instance)
+        connection.sync(self.rank_per_gpu_shm)
+        connection.Barrier()
+
+    def sync(self) -> None:
+        self.connection.sync(self.rank_per_gpu_shm)
+
+    def _istart_access_epoch(self, target_rank: int = 0) -> WorkerInfo:
+        return self.connection.Istart_access_epoch(target_rank)
+
+    def _iend_access_epoch(self, target_rank: int = 0) -> WorkerInfo:
+        return self.connection.Iend_access_epoch(target_rank)
+
+    def _finalize(self) -> None:
+        self.connection.Barrier()
+        self.connection.unlock_windows()
+        self.connection.finalize(self.arys)
+
+    def push_data(self) -> None:
+        cbs, compat = self.callbacks, self.compat
+        execute_callbacks("on_push_begin", callbacks=cbs, compat=compat)
+        while True:
+            execute_callbacks("global_shuffle", callbacks=cbs, compat=compat)
+            self.sync()
+            execute_callbacks("execute_function", callbacks=cbs, compat=compat)
+            self.iterations += 1
+            self.connection.heartbeat(self.rank_per_gpu_shm)
+            if self._iend_access_epoch() is WorkerInfo.STOP:
+                break
+            # the consumer reads the window here
+            if self._istart_access_epoch() is WorkerInfo.STOP:
+                break
+            execute_callbacks("on_shuffle_end", callbacks=cbs, compat=compat)
+        execute_callbacks("on_push_end", callbacks=cbs, compat=compat)
+        self._finalize()
+
+
+class DevicePusher:
+    """Producer role of the ``device`` transport: the reference's producer loop, unrolled into
+    stream-ordered steps (reference ddl/datapusher.py:46-170).
+
+    ``produce`` = global_shuffle -> sync -> execute_function -> offer (event on the side stream);
+    ``lend`` = the consumer's start_access_epoch; ``take_back`` = its end_access_epoch followed by
+    on_shuffle_end.  With a declared shuffle seed (or in trace mode) the next iteration is
+    produced while the consumer is still reading the current one (tables are double-buffered),
+    so even a single producer never stalls the consumer.
+    """
+
+    def __init__(self, connection: Connection, env, producer_idx: int):
+        self.connection, self.env = connection, env
+        self.cfg = connection.config
+        self.compat = self.cfg.compat == "as_wired"
+        self.producer_idx = int(producer_idx)  # 1-based, like the reference's shm rank
+        self.k = self.producer_idx - 1
+        self.rank_global = env.virtual_rank_global(self.producer_idx)
+        self.n_instance = env.n_instances
+        self.metadata_from_consumer: MetaData_Consumer_To_Producer = connection.recv_metadata_as_producer()
+        # every producer gets its own copy, as it would after pickling through MPI
+        pf = pickle.loads(pickle.dumps(self.metadata_from_consumer.producer_function))
+        self.producer_function = pf
+        self.callbacks: List[Any] = [pf]
+        self.on_init_return: DataProducerOnInitReturn = execute_callbacks(
+            "on_init", callbacks=self.callbacks, compat=self.compat, rank_global=self.rank_global)
+        self.metadata_to_consumer = _meta_from_init(self.on_init_return, self.metadata_from_consumer.batch_size)
+        connection.send_metadata(self.metadata_to_consumer, "producer")
+        self.engine = None
+        self.my_ary: Optional[np.ndarray] = None
+        self.global_shuffler = None
+        self.mode = "device"
+        self.iterations = 0
+        self._ready = None        # (table buffer, event) of the newest produced iteration
+        self._returned_ev = None  # consumer finished reading the previous iteration
+        self.lent_buf = 0
+        self._stopped = False
+
+    # -- set-up -----------------------------------------------------------------------------------------
+    def bind(self, engine) -> None:
+        """Second half of the reference constructor: window, shuffler, post_init, barrier."""
+        self.engine = engine
+        k, meta = self.k, self.metadata_from_consumer
+        mode = self.cfg.shuffle_mode
+        seed = self.metadata_to_consumer.shuffle_seed
+        if mode == "auto":
+            mode = "device" if seed is not None else "host"
+        if mode == "device" and seed is None:
+            raise ValueError("shuffle_mode='device' needs DataProducerOnInitReturn.shuffle_seed")
+        self.mode = mode
+        self.run_ahead = mode in ("device", "trace")
+
+        self.my_ary = engine.alloc_window(k)
+        num_exchange = int(self.on_init_return.nData * meta.global_shuffle_fraction_exchange)
+        if self.n_instance > 1 and num_exchange > 0:
+            if meta.global_shuffle_exchange_method != "sendrecv_replace":
+                raise NotImplementedError(f"{meta.global_shuffle_exchange_method} is not implemented")
+            if mode == "host":
+                from .shuffle import SendRecvReplaceGlobalShuffler
+
+                self.global_shuffler = SendRecvReplaceGlobalShuffler(
+                    self.my_ary, num_exchange, _TaggedComm(self.env.comm_nth_pusher, self.k), None,
+                    seed=self.producer_idx, n_instance=self.n_instance, my_index=self.env.color)
+            else:
+                self.global_shuffler = DeviceGlobalShuffler(engine, k, num_exchange, self.n_instance,
+                                                            self.env.color, seed=self.producer_idx)
+            self.callbacks.append(self.global_shuffler)
+        execute_callbacks("post_init", callbacks=self.callbacks, compat=self.compat, rank_global=self.rank_global,
+                          my_ary=self.my_ary, n_instance=self.n_instance)
+        engine.load_shard(k, self.my_ary)
+        engine.init_table(k, Pcg64(seed) if mode == "device" else None)
+        if mode == "trace":
+            self._proxy = np.arange(self.on_init_return.nData, dtype=np.int64).reshape(-1, 1)
+
+    def start(self) -> None:
+        execute_callbacks("on_push_begin", callbacks=self.callbacks, compat=self.compat)
+        self.produce()
+
+    # -- one producer iteration ---------------------------------------------------------------------------
+    def produce(self) -> None:
+        eng, k = self.engine, self.k
+        if self._returned_ev is not None:
+            eng.side.wait_event(self._returned_ev)  # the buffer about to be rewritten is no longer read
+        if self.mode == "host":
+            if eng.cuda:
+                eng.side.synchronize()  # the previous upload has left the pinned window
+            execute_callbacks("global_shuffle", callbacks=self.callbacks, compat=self.compat)
+            execute_callbacks("execute_function", callbacks=self.callbacks, compat=self.compat)
+            eng.load_shard(k, self.my_ary)
+        else:
+            before = eng.cur[k]
+            execute_callbacks("global_shuffle", callbacks=self.callbacks, compat=self.compat)
+            if eng.cur[k] == before:
+                eng.copy_forward(k)  # no exchange this iteration: still move to the other buffer
+            if self.mode == "device":
+                eng.local_shuffle(k)
+            else:
+                self._trace_shuffle()
+        ev = eng.event()
+        ev.record(eng.side) if eng.cuda else None
+        self._ready = (eng.cur[k], ev)
+        self.iterations += 1
+
+    def _trace_shuffle(self) -> None:
+        """Run the user's execute_function on a row-id proxy and apply the permutation it made."""
+        import torch
+
+        eng, k, pf = self.engine, self.k, self.producer_function
+        n = self.on_init_return.nData
+        self._proxy[:, 0] = np.arange(n, dtype=np.int64)
+        real, pf.my_ary = getattr(pf, "my_ary", None), self._proxy
+        try:
+            execute_callbacks("execute_function", callbacks=[pf], compat=self.compat)
+        finally:
+            pf.my_ary = real
+        perm = torch.from_numpy(self._proxy[:, 0].copy())
+        cur = eng.table(k)
+        with torch.cuda.stream(eng.side) if eng.cuda else _null():
+            perm_d = perm.to(eng.device, non_blocking=True)
+            cur.copy_(cur.index_select(0, perm_d))
+
+    # -- hand-over -------------------------------------------------------------------------------------------
+    def lend(self) -> None:
+        buf, ev = self._ready
+        eng = self.engine
+        eng.fetch.wait_event(ev)
+        self.lent_buf = buf
+        if self.run_ahead and not self._stopped:
+            self.produce()
+
+    def take_back(self) -> None:
+        eng = self.engine
+        ev = eng.event()
+        ev.record(eng.fetch) if eng.cuda else None
+        self._returned_ev = ev
+        execute_callbacks("on_shuffle_end", callbacks=self.callbacks, compat=self.compat)
+        if not self.run_ahead and not self._stopped:
+            self.produce()
+
+    def stop(self) -> None:
+        if not self._stopped:
+            self._stopped = True
+            execute_callbacks("on_push_end", callbacks=self.callbacks, compat=self.compat)
+
+    # -- checkpoint --------------------------------------------------------------------------------------------
+    def state_dict(self) -> dict:
+        eng, k = self.engine, self.k
+        if eng.cuda:
+            eng.side.synchronize()
+        d = {"iterations": self.iterations, "mode": self.mode,
+             "table": eng.table(k, self._ready[0]).cpu().numpy().copy(),
+             "rng_words": eng.states[k].cpu().numpy().copy()}
+        if self.global_shuffler is not None:
+            d["shuffler"] = self.global_shuffler.state_dict()
+        return d
+
+
+class _TaggedComm:
+    """comm_nth_pusher as seen by the k-th in-process producer: tags are offset per producer so
+    that several producers of one process can exchange concurrently without cross-talk."""
+
+    def __init__(self, comm, k: int):
+        self._c, self._off = comm, 1000 * (k + 1)
+
+    def Get_size(self):
+        return self._c.Get_size()
+
+    def Get_rank(self):
+        return self._c.Get_rank()
+
+    def sendrecv_replace(self, array, dest, source, sendtag=0, recvtag=0):
+        return self._c.sendrecv_replace(array, dest, source, sendtag + self._off, recvtag + self._off)
+
+
+class _null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False

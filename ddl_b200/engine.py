@@ -1,0 +1,382 @@
+"""Device transport engine: HBM shards, slot tables, streams and the batch ring.
+
+This is the B200-first data plane that replaces the reference's shared-memory windows and
+their physical shuffles (reference ddl/connection.py:88-139, ddl/datapusher.py:147-170).  The
+idea: **rows never move, indices do**.
+
+* Every producer's data is loaded once into an immutable *shard* in the symmetric heap
+  (HBM, mapped by every peer over NVLink).
+* Each reference "window" is a double-buffered *slot table* of 64-bit sample ids.  The global
+  shuffle (``index_exchange``) and the local shuffle (``perm_gen``) act on the table on a side
+  stream, one iteration ahead of the consumer.
+* A batch is assembled by one ``exchange_gather_collate`` launch on the fetch stream, straight
+  into one of ``ring_depth`` batch buffers, while the training stream works on the previous one.
+  Sample bytes cross NVLink exactly once, inside that kernel.
+
+With ``device.type == 'cpu'`` the same engine runs on POSIX shared memory and numpy/torch CPU
+ops; that is the executable model the multi-rank CPU tests use.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import logging
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _native as N
+from .config import LoaderConfig
+from .exceptions import DoesNotMatchError
+from .ops import tables as T
+from .ops.gather import SLOT_ROW_BITS, SLOT_ROW_MASK, Convert, GatherPlan, SourceTable, round_up
+from .ops.rng import Pcg64
+from .parallel.heap import SymmetricHeap
+
+log = logging.getLogger("ddl_b200")
+
+_TORCH_OF_NP = {np.dtype(np.float32): torch.float32, np.dtype(np.uint8): torch.uint8, np.dtype(np.int32): torch.int32,
+                np.dtype(np.int64): torch.int64, np.dtype(np.float16): torch.float16,
+                np.dtype(np.float64): torch.float64, np.dtype(np.int16): torch.int16, np.dtype(np.int8): torch.int8}
+
+
+class NullEvent:
+    def record(self, stream=None):
+        pass
+
+    def synchronize(self):
+        pass
+
+    def query(self):
+        return True
+
+    def elapsed_time(self, other):
+        return 0.0
+
+
+class NullStream:
+    cuda_stream = 0
+
+    def wait_event(self, ev):
+        pass
+
+    def wait_stream(self, s):
+        pass
+
+    def synchronize(self):
+        pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+class WindowSpec:
+    """Geometry of one producer's window, derived from its ``on_init`` answer."""
+
+    def __init__(self, meta):
+        self.nData = int(meta.nData)
+        self.nValues = int(meta.nValues)
+        self.np_dtype = np.dtype(meta.dtype if meta.dtype is not None else np.float32)
+        self.sample_bytes = self.nValues * self.np_dtype.itemsize
+        self.row_bytes = round_up(self.sample_bytes, 16)
+        self.convert: Convert = meta.convert if meta.convert is not None else Convert.copy()
+        self.splits = tuple(int(s) for s in meta.splits)
+        if self.convert.mode == N.CVT_COPY:
+            self.out_dtype = _TORCH_OF_NP[self.np_dtype]
+            self.out_elem = self.np_dtype.itemsize
+        else:
+            self.out_dtype = self.convert.out_dtype
+            self.out_elem = self.convert.out_elem_size
+            if self.convert.in_elem_size != self.np_dtype.itemsize:
+                raise ValueError(f"convert expects {self.convert.in_elem_size}-byte elements, window has {self.np_dtype}")
+        self.out_sample_bytes = self.nValues * self.out_elem
+        self.dst_row_bytes = round_up(self.out_sample_bytes, 16)
+        if sum(self.splits) != self.nValues:
+            raise DoesNotMatchError((self.splits, self.nValues), "splits must add up to nValues")
+
+    def key(self):
+        return (self.nData, self.sample_bytes, self.row_bytes, str(self.np_dtype), self.convert.mode)
+
+
+class CpuGather:
+    """CPU execution of exchange_gather_collate (vectorised numpy/torch), same semantics."""
+
+    def __init__(self, shards: Sequence[np.ndarray], spec: WindowSpec):
+        self.shards, self.spec = shards, spec
+
+    def run(self, slots: np.ndarray, out_raw: torch.Tensor) -> None:
+        sp = self.spec
+        slots = slots.astype(np.int64)
+        src = (slots >> SLOT_ROW_BITS) & 0xFFFF
+        row = slots & SLOT_ROW_MASK
+        raw = np.empty((slots.size, sp.sample_bytes), dtype=np.uint8)
+        for s in np.unique(src):
+            m = src == s
+            raw[m] = self.shards[int(s)][row[m], :sp.sample_bytes]
+        cv = sp.convert
+        dst = out_raw[:slots.size, :sp.out_sample_bytes]
+        if cv.mode == N.CVT_COPY:
+            dst.copy_(torch.from_numpy(raw))
+            return
+        in_np = {N.CVT_U8_BF16: np.uint8, N.CVT_U8_F32: np.uint8, N.CVT_F32_BF16: np.float32,
+                 N.CVT_I32_I64: np.int32}[cv.mode]
+        t = torch.from_numpy(raw.view(in_np))
+        if cv.mode == N.CVT_I32_I64:
+            y = t.to(torch.int64)
+        else:
+            n_elem = t.shape[1]
+            nch = len(cv.scale)
+            if nch > 1 and cv.chan_stride > 0:
+                ch = (torch.arange(n_elem) // cv.chan_stride) % nch
+                sc = torch.tensor(cv.scale, dtype=torch.float32)[ch]
+                bi = torch.tensor(cv.bias, dtype=torch.float32)[ch]
+            else:
+                sc = torch.tensor(cv.scale[0], dtype=torch.float32)
+                bi = torch.tensor(cv.bias[0], dtype=torch.float32)
+            y = (t.to(torch.float32) * sc + bi).to(cv.out_dtype)
+        dst.copy_(y.contiguous().view(torch.uint8).view(slots.size, -1))
+
+
+class DeviceEngine:
+    """Owns heap, shards, tables, RNG states, streams and gather plans of one consumer rank."""
+
+    def __init__(self, env, config: LoaderConfig, specs: List[WindowSpec], batch_size: int):
+        self.env, self.cfg, self.specs = env, config, specs
+        self.device = torch.device(env.device)
+        self.cuda = self.device.type == "cuda"
+        self.P = len(specs)
+        self.B = int(batch_size)
+        self.n_instances = env.n_instances
+        self.me = env.color
+        self.comm = env.comm_nth_pusher if env.transport == "device" else env.comm_global
+        self.launches = 0
+
+        # every instance must describe the same windows for the k-th producer (rows are swapped
+        # between them); the reference would fail inside MPI with a truncation error instead
+        keys = self.comm.allgather_obj([s.key() for s in specs])
+        for k in range(self.P):
+            if len({tuple(inst[k]) for inst in keys}) != 1:
+                raise DoesNotMatchError([inst[k] for inst in keys],
+                                        f"producer {k + 1}: window geometry differs between instances")
+
+        self.n_max = max(s.nData for s in specs)
+        self.heap = SymmetricHeap(self.comm, self.device)
+        self.shards = [self.heap.alloc(f"shard{k}", s.nData * s.row_bytes, zero=False) for k, s in enumerate(specs)]
+        self.tables_buf = self.heap.alloc("tables", self.P * 2 * self.n_max * 8)
+        self.flags_buf = self.heap.alloc("flags", 4096)
+        ring_row = max(s.dst_row_bytes for s in specs)
+        self.ring_depth = config.ring_depth
+        self.ring_buf = self.heap.alloc("ring", self.ring_depth * self.B * ring_row, zero=False)
+        self.heap.publish()
+
+        self.tables = self.tables_buf.tensor(torch.int64, (self.P, 2, self.n_max))
+        self.states = torch.zeros((self.P, 6), dtype=torch.int64, device=self.device)
+        self.cur = [0] * self.P  # buffer holding the newest produced iteration of window k
+        self.ring_row = ring_row
+        self.ring = [self.ring_buf.tensor(torch.uint8, (self.B, ring_row), i * self.B * ring_row)
+                     for i in range(self.ring_depth)]
+
+        if self.cuda:
+            self.main = torch.cuda.current_stream(self.device)
+            self.side = torch.cuda.Stream(self.device, priority=0)      # table production
+            self.fetch = torch.cuda.Stream(self.device, priority=-1)    # batch assembly
+        else:
+            self.main = self.side = self.fetch = NullStream()
+
+        # source table: id g = instance * P + k  ->  that instance's shard k
+        n_sources = self.n_instances * self.P
+        ptrs = [self.heap.peer_ptr(g // self.P, f"shard{g % self.P}") for g in range(n_sources)]
+        self.plans: List = []
+        if self.cuda:
+            self.sources = SourceTable(ptrs, self.device)
+            for s in specs:
+                self.plans.append(GatherPlan(self.sources, s.row_bytes, s.sample_bytes, s.convert,
+                                             dst_row_bytes=ring_row, variant=config.gather_variant,
+                                             max_ctas=config.gather_max_ctas, tune=config.gather_tune))
+        else:
+            for k, s in enumerate(specs):
+                views = [self.heap.peer_buffer(g // self.P, f"shard{g % self.P}").numpy(
+                    np.uint8, (specs[g % self.P].nData, specs[g % self.P].row_bytes)) for g in range(n_sources)]
+                self.plans.append(CpuGather(views, s))
+        self._barrier_epoch = 0
+        self._barrier_tensor = None
+        self._flag_pages = None
+        self._closed = False
+
+    # -- helpers --------------------------------------------------------------------------------
+    def event(self):
+        return torch.cuda.Event(enable_timing=self.cfg.trace) if self.cuda else NullEvent()
+
+    def source_id(self, k: int, instance: Optional[int] = None) -> int:
+        return (self.me if instance is None else instance) * self.P + k
+
+    def table(self, k: int, buf: Optional[int] = None) -> torch.Tensor:
+        return self.tables[k, self.cur[k] if buf is None else buf, :self.specs[k].nData]
+
+    def table_ptr(self, k: int, buf: int, first: int = 0) -> int:
+        return self.tables_buf.ptr + ((k * 2 + buf) * self.n_max + first) * 8
+
+    # -- K1 shard_load ----------------------------------------------------------------------------
+    def alloc_window(self, k: int) -> np.ndarray:
+        """Pinned host window handed to the user's post_init (reference: the MPI window)."""
+        s = self.specs[k]
+        if self.cuda:
+            buf, _ = self.heap.alloc_pinned(f"window{k}", s.nData * s.sample_bytes)
+            return buf.numpy(s.np_dtype, (s.nData, s.nValues))
+        return np.zeros((s.nData, s.nValues), dtype=s.np_dtype)
+
+    def load_shard(self, k: int, window: np.ndarray, stream=None) -> None:
+        """Copy a filled host window into the HBM shard (row stride padded to 16 bytes)."""
+        s = self.specs[k]
+        src = torch.from_numpy(window.reshape(s.nData, -1).view(np.uint8))
+        dst = self.shards[k].tensor(torch.uint8, (s.nData, s.row_bytes))
+        st = stream or self.side
+        if self.cuda:
+            with torch.cuda.stream(st):
+                if s.row_bytes == s.sample_bytes:
+                    dst.copy_(src, non_blocking=True)
+                else:
+                    dst[:, :s.sample_bytes].copy_(src, non_blocking=True)
+        else:
+            dst[:, :s.sample_bytes] = src
+
+    def load_shard_from_device(self, k: int, data: torch.Tensor) -> None:
+        """Fill shard k from a tensor that already lives on the device (synthetic benches)."""
+        s = self.specs[k]
+        dst = self.shards[k].tensor(torch.uint8, (s.nData, s.row_bytes))
+        src = data.reshape(s.nData, -1).view(torch.uint8)
+        with torch.cuda.stream(self.side) if self.cuda else NullStream():
+            dst[:, :s.sample_bytes].copy_(src)
+
+    # -- table production (side stream) -----------------------------------------------------------
+    def init_table(self, k: int, rng: Optional[Pcg64]) -> None:
+        self.cur[k] = 0
+        with torch.cuda.stream(self.side) if self.cuda else NullStream():
+            T.slot_iota(self.table(k, 0), self.source_id(k), 0, stream=self.side if self.cuda else None)
+            if rng is not None:
+                self.states[k].copy_(torch.from_numpy(rng.to_words()))
+
+    def stream_barrier(self) -> None:
+        """All consumers' side streams meet here (orders table reads/writes across GPUs)."""
+        if self.n_instances == 1:
+            return
+        mode = self.cfg.barrier
+        if mode == "auto":
+            mode = "nccl" if self.cuda and _nccl_ready() else "host"
+        if mode == "nccl":
+            import torch.distributed as dist
+
+            if self._barrier_tensor is None:
+                self._barrier_tensor = torch.zeros(1, device=self.device)
+            with torch.cuda.stream(self.side):
+                dist.all_reduce(self._barrier_tensor, group=self.env.consumer_group)
+        elif mode == "flags":
+            self._flag_barrier()
+        else:
+            self.side.synchronize()
+            self.comm.barrier()
+
+    def _flag_barrier(self) -> None:
+        if self._flag_pages is None:
+            pages = [self.heap.peer_ptr(r, "flags") for r in range(self.n_instances)]
+            self._flag_pages = torch.tensor(pages, dtype=torch.int64).to(self.device)
+            self._flag_status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._barrier_epoch += 1
+        polls = int(self.cfg.timeout_s * 2e6)
+        N.check(N.lib().bddl_flag_barrier(self._flag_pages.data_ptr(), self.n_instances, self.me,
+                                          self._barrier_epoch, polls, None, self._flag_status.data_ptr(),
+                                          C.c_void_p(self.side.cuda_stream)))
+        self.launches += 1
+
+    def exchange_tables(self, k: int, send_to: int, recv_from: int, num_exchange: int) -> None:
+        """index_exchange for window k: next table = own with the leading rows taken from the
+        partners' current tables (reference ddl/shuffle.py:92-108 in index space)."""
+        cur, nxt = self.cur[k], 1 - self.cur[k]
+        n = self.specs[k].nData
+        active = num_exchange > 0 and self.n_instances > 1
+        if active:
+            self.stream_barrier()  # partners' current tables are complete; nobody reads `nxt` any more
+        own = self.table(k, cur)
+        dst = self.table(k, nxt)
+        if self.cuda:
+            fr = self.heap.peer_ptr(recv_from, "tables") + ((k * 2 + cur) * self.n_max) * 8 if active else None
+            fs = self.heap.peer_ptr(send_to, "tables") + ((k * 2 + cur) * self.n_max) * 8 if active else None
+            with torch.cuda.stream(self.side):
+                T.index_exchange(dst, own, None, None, num_exchange if active else 0, stream=self.side,
+                                 from_recv_ptr=fr, from_send_ptr=fs)
+            self.launches += 1
+        else:
+            if active:
+                fr = self.heap.peer_buffer(recv_from, "tables").tensor(torch.int64, (self.P, 2, self.n_max))[k, cur, :n]
+                fs = self.heap.peer_buffer(send_to, "tables").tensor(torch.int64, (self.P, 2, self.n_max))[k, cur, :n]
+                T.index_exchange(dst, own, fr, fs, num_exchange)
+            else:
+                T.index_exchange(dst, own, None, None, 0)
+        self.cur[k] = nxt
+
+    def copy_forward(self, k: int) -> None:
+        self.exchange_tables(k, self.me, self.me, 0)
+
+    def local_shuffle(self, k: int) -> None:
+        """perm_gen on the newest table of window k (reference tests/run_ddl.py:163-167)."""
+        n = self.specs[k].nData
+        tbl = self.tables[k, self.cur[k]].unsqueeze(0)
+        st = self.states[k].unsqueeze(0)
+        if self.cuda:
+            with torch.cuda.stream(self.side):
+                T.perm_gen(tbl, st, n=n, stream=self.side)
+            self.launches += 1
+        else:
+            T.perm_gen(tbl, st, n=n)
+
+    def upload_table(self, k: int, slots: np.ndarray) -> None:
+        """Install a host-computed table (trace mode / checkpoint restore) into the next buffer."""
+        nxt = 1 - self.cur[k]
+        t = torch.from_numpy(np.ascontiguousarray(slots, dtype=np.int64))
+        with torch.cuda.stream(self.side) if self.cuda else NullStream():
+            self.table(k, nxt).copy_(t, non_blocking=True)
+        self.cur[k] = nxt
+
+    # -- batch assembly (fetch stream) --------------------------------------------------------------
+    def gather(self, k: int, buf: int, first_row: int, ring_slot: int, n: Optional[int] = None) -> None:
+        n = self.B if n is None else n
+        if self.cuda:
+            self.plans[k].run_ptr(self.table_ptr(k, buf, first_row), self.ring[ring_slot].data_ptr(), n,
+                                  self.fetch.cuda_stream)
+            self.launches += 1
+        else:
+            slots = self.tables[k, buf, first_row:first_row + n].numpy()
+            self.plans[k].run(slots, self.ring[ring_slot])
+
+    def batch_views(self, k: int, ring_slot: int):
+        """Typed [B, nValues] view of a ring slot, split into the sample's fields (dim=1)."""
+        s = self.specs[k]
+        raw = self.ring[ring_slot]
+        typed = raw if s.out_dtype == torch.uint8 else raw.view(s.out_dtype)
+        typed = typed[:, :s.nValues]
+        return torch.split(typed, list(s.splits), dim=1)
+
+    # -- teardown -------------------------------------------------------------------------------------
+    def close(self) -> None:
+        if self._closed:
+            return
+        self._closed = True
+        if self.cuda:
+            torch.cuda.synchronize(self.device)
+        self.comm.barrier()
+        self.tables = None
+        self.ring = []
+        self.plans = []
+        self.heap.close()
+
+
+def _nccl_ready() -> bool:
+    try:
+        import torch.distributed as dist
+
+        return dist.is_initialized() and dist.is_nccl_available() and "nccl" in str(dist.get_backend()).lower()
+    except Exception:
+        return False

@@ -1,0 +1,193 @@
+"""Symmetric heap: named buffers every rank allocates and every peer can address.
+
+The reference maps every producer's float32 array into all ranks of an instance with MPI-3
+shared-memory windows (``Win.Allocate_shared`` + ``Shared_query``,
+reference ddl/connection.py:88-139).  Here:
+
+* on a GPU each rank ``cudaMalloc``s its buffers through the native library and publishes CUDA
+  IPC handles over the control plane; peers map them, after which a kernel reaches remote
+  shards, slot tables and batch buffers through NVLink with ordinary pointers;
+* on the CPU (tests, the CPU execution path) the buffers are POSIX shared memory, so the same
+  multi-rank logic runs without a GPU;
+* ranks that share a process (threads in tests, emulated ranks on one GPU) skip the handle
+  export and use each other's pointers directly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import uuid
+from typing import Dict, List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from .. import _native as N
+from .comm import Comm
+
+
+class _CudaView:
+    """Minimal ``__cuda_array_interface__`` carrier so torch can alias native memory."""
+
+    def __init__(self, ptr: int, nbytes: int, owner):
+        self.owner = owner
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class Buffer:
+    """One heap allocation: raw address + typed views."""
+
+    def __init__(self, name: str, ptr: int, nbytes: int, device: torch.device, keep=None, shm_name: str = ""):
+        self.name, self.ptr, self.nbytes, self.device = name, int(ptr), int(nbytes), device
+        self._keep = keep
+        self.shm_name = shm_name
+        self._u8: Optional[torch.Tensor] = None
+
+    def bytes(self) -> torch.Tensor:
+        """The whole buffer as a uint8 tensor on its device (aliases the memory)."""
+        if self._u8 is None:
+            if self.device.type == "cuda":
+                self._u8 = torch.as_tensor(_CudaView(self.ptr, self.nbytes, self), device=self.device)
+            else:
+                arr = np.ctypeslib.as_array((C.c_uint8 * self.nbytes).from_address(self.ptr))
+                self._u8 = torch.from_numpy(arr)
+        return self._u8
+
+    def tensor(self, dtype: torch.dtype, shape, offset_bytes: int = 0) -> torch.Tensor:
+        n = int(np.prod(shape)) * torch.empty((), dtype=dtype).element_size()
+        return self.bytes()[offset_bytes:offset_bytes + n].view(dtype).view(*shape)
+
+    def numpy(self, dtype=np.uint8, shape=None, offset_bytes: int = 0) -> np.ndarray:
+        if self.device.type != "cpu":
+            raise ValueError("numpy views exist for host buffers only")
+        dt = np.dtype(dtype)
+        count = (self.nbytes - offset_bytes) // dt.itemsize if shape is None else int(np.prod(shape))
+        arr = np.ctypeslib.as_array((C.c_uint8 * (count * dt.itemsize)).from_address(self.ptr + offset_bytes))
+        arr = arr.view(dt)
+        return arr if shape is None else arr.reshape(shape)
+
+
+class SymmetricHeap:
+    """Per-rank allocator + peer address table.  ``alloc`` then ``publish`` (collective)."""
+
+    def __init__(self, comm: Comm, device: torch.device):
+        self.comm = comm
+        self.device = torch.device(device)
+        self.local: Dict[str, Buffer] = {}
+        self.peers: Dict[Tuple[int, str], Tuple[int, int]] = {}  # (rank, name) -> (ptr, nbytes)
+        self._opened: List[int] = []
+        self._attached: List[Tuple[int, int]] = []
+        self._session = comm.bcast_obj(uuid.uuid4().hex[:12] if comm.rank == 0 else None, 0)
+        self._closed = False
+        if self.device.type == "cuda":
+            N.check(N.lib().bddl_set_device(self.device.index or 0))
+
+    # -- allocation -----------------------------------------------------------------------------
+    def alloc(self, name: str, nbytes: int, zero: bool = True) -> Buffer:
+        if name in self.local:
+            raise ValueError(f"heap buffer {name!r} exists")
+        nbytes = max(16, (int(nbytes) + 255) // 256 * 256)
+        lib = N.lib()
+        p = C.c_void_p()
+        if self.device.type == "cuda":
+            N.check(lib.bddl_set_device(self.device.index or 0))
+            N.check(lib.bddl_malloc(C.byref(p), nbytes))
+            buf = Buffer(name, p.value, nbytes, self.device)
+            if zero:
+                buf.bytes().zero_()
+        else:
+            shm = f"/bddl_{self._session}_{self.comm.world_rank}_{len(self.local)}"
+            N.check(lib.bddl_shm_create(shm.encode(), nbytes, C.byref(p)))
+            buf = Buffer(name, p.value, nbytes, self.device, shm_name=shm)
+        self.local[name] = buf
+        return buf
+
+    def alloc_pinned(self, name: str, nbytes: int) -> Tuple[Buffer, int]:
+        """Pinned host memory mapped into the device: (host buffer, device-visible address)."""
+        nbytes = max(16, int(nbytes))
+        h, d = C.c_void_p(), C.c_void_p()
+        N.check(N.lib().bddl_host_alloc(C.byref(h), C.byref(d), nbytes))
+        buf = Buffer(name, h.value, nbytes, torch.device("cpu"), keep=("pinned", h.value))
+        self.local[name] = buf
+        return buf, int(d.value)
+
+    # -- exchange -------------------------------------------------------------------------------
+    def publish(self) -> None:
+        """Collective: make every local buffer addressable by every peer."""
+        lib = N.lib()
+        mine = {}
+        for name, b in self.local.items():
+            if b._keep is not None:
+                continue  # pinned host staging is private
+            if self.device.type == "cuda":
+                h = (C.c_uint8 * 64)()
+                N.check(lib.bddl_ipc_get_handle(C.c_void_p(b.ptr), h))
+                mine[name] = ("ipc", bytes(h), b.nbytes, b.ptr, os.getpid(), self.device.index or 0)
+            else:
+                mine[name] = ("shm", b.shm_name, b.nbytes, b.ptr, os.getpid(), -1)
+        table = self.comm.allgather_obj(mine)
+        for r, entries in enumerate(table):
+            for name, (kind, handle, nbytes, ptr, pid, dev) in entries.items():
+                if (r, name) in self.peers:
+                    continue
+                if r == self.comm.rank or pid == os.getpid() and (kind == "shm" or dev == (self.device.index or 0)):
+                    self.peers[(r, name)] = (ptr, nbytes)
+                elif kind == "ipc":
+                    if pid == os.getpid():
+                        # another device driven by this process: direct peer access
+                        N.check(lib.bddl_enable_peer_access(dev))
+                        self.peers[(r, name)] = (ptr, nbytes)
+                        continue
+                    p = C.c_void_p()
+                    hb = (C.c_uint8 * 64).from_buffer_copy(handle)
+                    N.check(lib.bddl_ipc_open_handle(hb, C.byref(p)))
+                    self._opened.append(p.value)
+                    self.peers[(r, name)] = (p.value, nbytes)
+                else:
+                    p = C.c_void_p()
+                    N.check(lib.bddl_shm_attach(handle.encode(), nbytes, C.byref(p)))
+                    self._attached.append((p.value, nbytes))
+                    self.peers[(r, name)] = (p.value, nbytes)
+        self.comm.barrier()
+        # names can go once everybody is attached; the memory lives until the last unmap
+        if self.device.type == "cpu":
+            for b in self.local.values():
+                if b.shm_name:
+                    lib.bddl_shm_unlink(b.shm_name.encode())
+                    b.shm_name = ""
+
+    def peer_ptr(self, rank: int, name: str) -> int:
+        return self.peers[(rank, name)][0]
+
+    def peer_buffer(self, rank: int, name: str) -> Buffer:
+        """A peer's buffer as a local object (CPU heaps and same-process peers only)."""
+        ptr, nbytes = self.peers[(rank, name)]
+        return Buffer(name, ptr, nbytes, self.device, keep=("peer", rank))
+
+    # -- teardown -------------------------------------------------------------------------------
+    def close(self) -> None:
+        if self._closed:
+            return
+        self._closed = True
+        lib = N.lib()
+        if self.device.type == "cuda":
+            try:
+                torch.cuda.synchronize(self.device)
+            except Exception:
+                pass
+        for p in self._opened:
+            lib.bddl_ipc_close_handle(C.c_void_p(p))
+        for p, n in self._attached:
+            lib.bddl_shm_detach(C.c_void_p(p), n)
+        for b in self.local.values():
+            b._u8 = None
+            if b._keep is not None and b._keep[0] == "pinned":
+                lib.bddl_host_free(C.c_void_p(b.ptr))
+            elif self.device.type == "cuda":
+                lib.bddl_free(C.c_void_p(b.ptr))
+            else:
+                if b.shm_name:
+                    lib.bddl_shm_unlink(b.shm_name.encode())
+                lib.bddl_shm_detach(C.c_void_p(b.ptr), b.nbytes)
+        self.local.clear()
+        self.peers.clear()

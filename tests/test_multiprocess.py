@@ -1,0 +1,83 @@
+"""Multi-process runs of the whole loader on the CPU (gloo rendezvous, world_size > 1), the
+counterpart of the reference's only test (reference tests/test_ddl.py:8-28: mpirun -np 4, exit
+code 0) -- but with assertions on *what* arrives: every consumer must see exactly the sample
+order the reference semantics prescribe (tests/oracle.py)."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import expected_epochs
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+WORKER = os.path.join(HERE, "workers", "run_loader.py")
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def run_world(nproc, cfg, tmp_path, timeout=150, extra_env=None):
+    cfg = dict(cfg, out=str(tmp_path))
+    env = dict(os.environ, BDDL_TEST_CFG=json.dumps(cfg), OMP_NUM_THREADS="1")
+    env.update(extra_env or {})
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), WORKER]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    return res
+
+
+def check(tmp_path, n_instances, P, cfg, designed=True):
+    exp = expected_epochs(n_instances, P, cfg["n"], cfg["B"], cfg["epochs"], cfg.get("fraction", 0.0), designed)
+    for i in range(n_instances):
+        got = np.load(os.path.join(str(tmp_path), f"seen_{i}.npy"))
+        assert got.shape == exp[i].shape
+        assert np.array_equal(got, exp[i]), f"instance {i}: order differs from the reference semantics"
+
+
+@pytest.mark.timeout(200)
+def test_process_transport_like_reference_test(tmp_path):
+    """1 consumer + 3 producer processes, the reference's own layout (tests/run_ddl.py:301-316)."""
+    cfg = {"n_instances": 1, "n": 5000, "v": 9, "B": 512, "epochs": 5, "fraction": 0.5}
+    run_world(4, cfg, tmp_path)
+    check(tmp_path, 1, 3, cfg)
+
+
+@pytest.mark.timeout(200)
+def test_process_transport_two_instances_global_shuffle(tmp_path):
+    """2 instances x (1 consumer + 1 producer): the exchange the reference designed but never runs."""
+    cfg = {"n_instances": 2, "n": 2000, "v": 4, "B": 256, "epochs": 4, "fraction": 0.5}
+    run_world(4, cfg, tmp_path)
+    check(tmp_path, 2, 1, cfg)
+
+
+@pytest.mark.timeout(200)
+def test_process_transport_as_wired_has_no_exchange(tmp_path):
+    cfg = {"n_instances": 2, "n": 2000, "v": 4, "B": 256, "epochs": 3, "fraction": 0.5, "compat": "as_wired"}
+    run_world(4, cfg, tmp_path)
+    check(tmp_path, 2, 1, cfg, designed=False)
+
+
+@pytest.mark.timeout(200)
+@pytest.mark.parametrize("mode,declare", [("device", True), ("trace", False), ("host", False)])
+def test_device_transport_three_instances(tmp_path, mode, declare):
+    """One process per instance, in-process producers, slot-table exchange over shared memory."""
+    cfg = {"n_instances": 3, "n_producers": 2, "n": 1500, "v": 5, "B": 128, "epochs": 6, "fraction": 0.5,
+           "shuffle_mode": mode, "declare_seed": declare}
+    run_world(3, cfg, tmp_path)
+    check(tmp_path, 3, 2, cfg)
+
+
+@pytest.mark.timeout(200)
+def test_device_transport_four_instances_single_producer(tmp_path):
+    cfg = {"n_instances": 4, "n_producers": 1, "n": 1000, "v": 3, "B": 100, "epochs": 4, "fraction": 0.3,
+           "shuffle_mode": "device", "declare_seed": True}
+    run_world(4, cfg, tmp_path)
+    check(tmp_path, 4, 1, cfg)

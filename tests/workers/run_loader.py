@@ -1,0 +1,62 @@
+"""Worker program for the multi-process loader tests (the analogue of the reference's
+tests/run_ddl.py:107-240): every sample's first value is its global id, so the order in which
+batches arrive can be compared with an oracle.  Launched under torch.distributed.run."""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import ddl_b200 as ddl  # noqa: E402
+
+CFG = json.loads(os.environ["BDDL_TEST_CFG"])
+
+
+class IdProducer(ddl.ProducerFunctionSkeleton):
+    def __init__(self, n, v, declare_seed, group_size):
+        super().__init__()
+        self.n, self.v, self.declare_seed, self.group_size = n, v, declare_seed, group_size
+        self.rng = None
+
+    def on_init(self, **kw):
+        super().on_init(**kw)
+        self.rng = np.random.default_rng(seed=self.rank_global)
+        return ddl.DataProducerOnInitReturn(self.n, self.v, (self.n, self.v), (1, self.v - 1),
+                                            shuffle_seed=self.rank_global if self.declare_seed else None)
+
+    def post_init(self, **kw):
+        self.my_ary = kw["my_ary"]
+        gid = self.rank_global * 1_000_000 + np.arange(self.n)
+        self.my_ary[:, 0] = gid.astype(np.float32)
+        self.my_ary[:, 1:] = (gid[:, None] % 97).astype(np.float32)
+
+    def execute_function(self, **kw):
+        self.rng.shuffle(self.my_ary)
+
+
+def body(env, conn):
+    n, v, B, E = CFG["n"], CFG["v"], CFG["B"], CFG["epochs"]
+    group_size = env.n_producers + 1
+    loader = ddl.DistributedDataLoader(IdProducer(n, v, CFG.get("declare_seed", False), group_size), B, conn, E,
+                                       CFG.get("fraction", 0.0), "sendrecv_replace", env.color, env.n_instances)
+    seen = []
+    for e in range(E):
+        ids = []
+        for i, (a, b) in enumerate(loader):
+            assert a.shape == (B, 1) and b.shape == (B, v - 1)
+            ids.append(a.detach().cpu().numpy()[:, 0].astype(np.int64))
+            assert np.array_equal(b.cpu().numpy()[:, 0].astype(np.int64), ids[-1] % 97)
+            loader.mark(ddl.Marker.END_OF_BATCH)
+        loader.mark(ddl.Marker.END_OF_EPOCH)
+        seen.append(np.concatenate(ids))
+    np.save(os.path.join(CFG["out"], f"seen_{env.color}.npy"), np.stack(seen))
+
+
+if __name__ == "__main__":
+    cfg = ddl.LoaderConfig.from_env(compat=CFG.get("compat"), shuffle_mode=CFG.get("shuffle_mode"),
+                                    timeout_s=CFG.get("timeout_s", 120.0))
+    main = ddl.distributed_dataloader(body, n_instances=CFG["n_instances"], n_producers=CFG.get("n_producers"),
+                                      config=cfg, device="cpu" if CFG.get("cpu", True) else None)
+    main()
