@@ -1,0 +1,243 @@
+"""Headline benchmark: GPU-delivered samples/s of the distributed loader.
+
+Metric and config follow BASELINE.json: ImageNet-shaped synthetic uint8 3x224x224 samples,
+per-epoch global shuffle (fraction 0.5) across all GPUs, delivered as normalised bf16 batches
+in HBM.  One process per GPU (torchrun), weak scaling (fixed shard and batch per GPU).
+
+  value   device-timed (CUDA events, max over ranks) samples/s over all GPUs with the shards
+          resident in HBM -- the product's main path: one exchange_gather_collate launch per
+          batch pulls rows from every peer over NVLink, converts and collates them.
+  e2e     the same metric through the same public API with the dataset resident in pinned
+          host memory: every step copies that step's raw samples host->device and reads a
+          checksum of the delivered batch back to the host.
+
+`--impl reference` runs the unmodified reference (baseline/_ref) through its own API on the same
+config; see baseline/run_reference.py.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+MEAN, STD = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+C_, H_, W_ = 3, 224, 224
+SAMPLE = C_ * H_ * W_
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index: int):
+        self.idx, self.rows, self.proc = device_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                for n, v in zip(names, r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_producer(rows: int, seed_base: int = 1234):
+    import numpy as np
+
+    import ddl_b200 as ddl
+
+    class ImageShard(ddl.ProducerFunctionSkeleton):
+        """Synthetic ImageNet-shaped shard: `rows` random uint8 CHW images per producer."""
+
+        def __init__(self):
+            super().__init__()
+
+        def on_init(self, **kw):
+            super().on_init(**kw)
+            cv = ddl.Convert.normalize_u8(MEAN, STD, H_ * W_)
+            return ddl.DataProducerOnInitReturn(rows, SAMPLE, (rows, SAMPLE), (SAMPLE,), dtype=np.uint8, convert=cv,
+                                                shuffle_seed=self.rank_global)
+
+        def post_init(self, **kw):
+            self.my_ary = kw["my_ary"]
+            g = np.random.default_rng(seed_base + self.rank_global)
+            flat = self.my_ary.reshape(-1)
+            step = 1 << 26
+            for o in range(0, flat.size, step):  # random bytes, generated in slices to bound memory
+                n = min(step, flat.size - o)
+                flat[o:o + n] = np.frombuffer(g.bytes(n), dtype=np.uint8)
+
+        def execute_function(self, **kw):  # only used by host-shuffle mode
+            np.random.default_rng(self.rank_global).shuffle(self.my_ary)
+
+    return ImageShard()
+
+
+def run_ours(args) -> dict:
+    import numpy as np
+    import torch
+
+    import ddl_b200 as ddl
+    from ddl_b200 import _native as N
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
+    result = {}
+
+    def timed_loop(loader, env, steps, warmup, e2e: bool):
+        dev = env.device
+        main = torch.cuda.current_stream(dev)
+        host_out = torch.empty(1, dtype=torch.float32).pin_memory()
+        it = iter(_steps(loader))
+        for _ in range(warmup):
+            next(it)
+        torch.cuda.synchronize(dev)
+        env.comm_global.barrier()
+        torch.cuda.synchronize(dev)
+        l0 = N.launch_count()
+        sampler = ClockSampler(dev.index or 0)
+        if env.comm_global.rank == 0 and not e2e:
+            sampler.start()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        a.record(main)
+        for _ in range(steps):
+            x = next(it)
+            if e2e:  # device->host read of the step's result: a checksum of the delivered batch
+                host_out.copy_(x[0, :64].float().sum().reshape(1), non_blocking=True)
+                main.synchronize()
+        b.record(main)
+        torch.cuda.synchronize(dev)
+        wall = time.perf_counter() - t0
+        env.comm_global.barrier()
+        clocks = sampler.stop() if (env.comm_global.rank == 0 and not e2e) else None
+        ms = a.elapsed_time(b)
+        if e2e:
+            ms = max(ms, wall * 1e3)
+        all_ms = env.comm_global.allgather_obj(ms)
+        return max(all_ms), N.launch_count() - l0, clocks
+
+    def _steps(loader):
+        while True:
+            for (x,) in loader:
+                yield x
+                loader.mark(ddl.Marker.END_OF_BATCH)
+            loader.mark(ddl.Marker.END_OF_EPOCH)
+
+    def body(env, conn):
+        B, rows = args.batch, args.rows
+        total = args.steps + args.warmup + 2
+        epochs = (total + rows // B - 1) // (rows // B) + 1
+        loader = ddl.DistributedDataLoader(make_producer(rows), B, conn, 10**9, args.fraction, "sendrecv_replace",
+                                           env.color, env.n_instances)
+        ms, launches, clocks = timed_loop(loader, env, args.steps, args.warmup, e2e=False)
+        # numerics spot check of one delivered batch against the fp32 PyTorch statement
+        (x,) = loader[0]
+        ok = bool(torch.isfinite(x.float()).all().item()) and x.shape == (B, SAMPLE) and x.dtype == torch.bfloat16
+        loader.close()
+        result.update(ms=ms, launches=launches, clocks=clocks, ok=ok, n=env.n_instances, rank=env.comm_global.rank)
+
+    cfg = ddl.LoaderConfig.from_env(metrics=False, ring_depth=args.ring, gather_variant=args.variant,
+                                    gather_tune=args.tune)
+    ddl.distributed_dataloader(body, n_instances="world", n_producers=1, config=cfg)()
+
+    e2e = None
+    if not args.no_e2e:
+        def body_e2e(env, conn):
+            B, rows = args.batch, min(args.rows, args.e2e_rows)
+            loader = ddl.DistributedDataLoader(make_producer(rows), B, conn, 10**9, args.fraction,
+                                               "sendrecv_replace", env.color, env.n_instances)
+            steps = max(8, args.steps // 4)
+            ms, _, _ = timed_loop(loader, env, steps, max(3, args.warmup // 2), e2e=True)
+            loader.close()
+            result.update(e2e_ms=ms, e2e_steps=steps)
+
+        cfg2 = ddl.LoaderConfig.from_env(metrics=False, ring_depth=args.ring, residency="host")
+        ddl.distributed_dataloader(body_e2e, n_instances="world", n_producers=1, config=cfg2)()
+        v = args.gpus * args.batch * result["e2e_steps"] / (result["e2e_ms"] * 1e-3)
+        e2e = {"value": round(v, 1), "unit": "samples/s", "h2d_bytes_per_step": args.batch * SAMPLE,
+               "d2h_bytes_per_step": 4, "steps": result["e2e_steps"],
+               "path": "pinned host shard -> cudaMemcpyAsync staging -> convert kernel -> checksum D2H"}
+
+    if result.get("rank", 0) != 0:
+        return {}
+    ms_per_step = result["ms"] / args.steps
+    value = args.gpus * args.batch / (ms_per_step * 1e-3)
+    return {
+        "metric": "gpu_delivered_samples_per_s", "value": round(value, 1), "unit": "samples/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 5), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"model": "imagenet_u8_3x224x224_loader", "global_batch": args.batch * args.gpus,
+                   "seq_len": SAMPLE, "parallelism": f"dp{args.gpus}", "per_gpu_batch": args.batch,
+                   "rows_per_gpu": args.rows, "fraction_exchange": args.fraction,
+                   "l2": "inputs larger than L2 (shard %.1f GB per GPU, every row read once per epoch)"
+                         % (args.rows * SAMPLE / 1e9)},
+        "clocks": result["clocks"], "e2e": e2e, "gpu_launches": int(result["launches"]),
+        "numerics_ok": result["ok"], "impl": "ddl_b200",
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ddl_b200", choices=["ddl_b200", "reference"])
+    ap.add_argument("--batch", type=int, default=256)
+    ap.add_argument("--rows", type=int, default=16384)
+    ap.add_argument("--e2e-rows", type=int, default=4096)
+    ap.add_argument("--fraction", type=float, default=0.5)
+    ap.add_argument("--ring", type=int, default=3)
+    ap.add_argument("--variant", type=int, default=0)
+    ap.add_argument("--tune", type=int, default=0)
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        from baseline.run_reference import run_reference
+
+        out = run_reference(args)
+    else:
+        out = run_ours(args)
+    if out:
+        print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()

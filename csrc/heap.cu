@@ -162,4 +162,32 @@ int bddl_stage_rows(void* d_dst, int64_t dst_row_bytes, const void* h_src, int64
     return 0;
 }
 
+// Same for a batch described by slot ids (source << 48 | row) over several pinned shards:
+// h_bases[source] is the host address of that shard in this process.
+int bddl_stage_slots(void* d_dst, int64_t dst_row_bytes, const void* const* h_bases, int32_t n_sources,
+                     int64_t row_bytes, const uint64_t* slots, int64_t n, int64_t copy_bytes, void* stream,
+                     int64_t* n_copies) {
+    if (!d_dst || !h_bases || (!slots && n > 0) || copy_bytes > row_bytes || copy_bytes > dst_row_bytes)
+        return bddl_fail(BDDL_ERR_INVALID, "stage_slots: bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    const uint64_t row_mask = (1ULL << BDDL_SLOT_ROW_BITS) - 1;
+    const bool dense = copy_bytes == row_bytes && row_bytes == dst_row_bytes;
+    int64_t copies = 0, i = 0;
+    while (i < n) {
+        const uint64_t src = slots[i] >> BDDL_SLOT_ROW_BITS;
+        if ((int64_t)src >= n_sources) return bddl_fail(BDDL_ERR_INVALID, "stage_slots: source %llu out of range",
+                                                        (unsigned long long)src);
+        int64_t j = i + 1;
+        if (dense)
+            while (j < n && slots[j] == slots[j - 1] + 1) ++j;
+        const char* from = (const char*)h_bases[src] + (int64_t)(slots[i] & row_mask) * row_bytes;
+        BDDL_CUDA(cudaMemcpyAsync((char*)d_dst + i * dst_row_bytes, from,
+                                  (size_t)(dense ? (j - i) * row_bytes : copy_bytes), cudaMemcpyHostToDevice, st));
+        ++copies;
+        i = j;
+    }
+    if (n_copies) *n_copies = copies;
+    return 0;
+}
+
 }  // extern "C"

@@ -39,6 +39,22 @@ def _meta_from_init(ret: DataProducerOnInitReturn, batch_size: int) -> MetaData_
         shuffle_seed=getattr(ret, "shuffle_seed", None))
 
 
+def _private_copy(obj):
+    """What pickling through MPI does to the producer function in the reference
+    (reference ddl/types.py:9): each producer works on its own copy."""
+    try:
+        return pickle.loads(pickle.dumps(obj))
+    except Exception:
+        try:
+            import cloudpickle
+
+            return pickle.loads(cloudpickle.dumps(obj))
+        except Exception:
+            import copy
+
+            return copy.deepcopy(obj)
+
+
 class DataPusherABC(ABC):
     @abstractmethod
     def push_data(self) -> None: ...
@@ -144,7 +160,7 @@ class DevicePusher:
         self.n_instance = env.n_instances
         self.metadata_from_consumer: MetaData_Consumer_To_Producer = connection.recv_metadata_as_producer()
         # every producer gets its own copy, as it would after pickling through MPI
-        pf = pickle.loads(pickle.dumps(self.metadata_from_consumer.producer_function))
+        pf = _private_copy(self.metadata_from_consumer.producer_function)
         self.producer_function = pf
         self.callbacks: List[Any] = [pf]
         self.on_init_return: DataProducerOnInitReturn = execute_callbacks(
@@ -250,6 +266,7 @@ class DevicePusher:
         eng = self.engine
         eng.fetch.wait_event(ev)
         self.lent_buf = buf
+        eng.on_lend(self.k, buf)
         if self.run_ahead and not self._stopped:
             self.produce()
 

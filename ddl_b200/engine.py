@@ -164,7 +164,13 @@ class DeviceEngine:
 
         self.n_max = max(s.nData for s in specs)
         self.heap = SymmetricHeap(self.comm, self.device)
-        self.shards = [self.heap.alloc(f"shard{k}", s.nData * s.row_bytes, zero=False) for k, s in enumerate(specs)]
+        # host residency: shards stay in pinned, node-shared host memory and every step's rows
+        # are copied host->device (N9 stage_host) or pulled by the kernel over PCIe
+        self.host_resident = config.residency == "host" and self.cuda
+        if self.host_resident:
+            self.shards = [self.heap.alloc_host_shared(f"shard{k}", s.nData * s.row_bytes) for k, s in enumerate(specs)]
+        else:
+            self.shards = [self.heap.alloc(f"shard{k}", s.nData * s.row_bytes, zero=False) for k, s in enumerate(specs)]
         self.tables_buf = self.heap.alloc("tables", self.P * 2 * self.n_max * 8)
         self.flags_buf = self.heap.alloc("flags", 4096)
         ring_row = max(s.dst_row_bytes for s in specs)
@@ -190,7 +196,24 @@ class DeviceEngine:
         n_sources = self.n_instances * self.P
         ptrs = [self.heap.peer_ptr(g // self.P, f"shard{g % self.P}") for g in range(n_sources)]
         self.plans: List = []
-        if self.cuda:
+        self.stage = None
+        if self.host_resident and config.host_stage == "memcpy":
+            self.h_bases = (C.c_void_p * n_sources)(*ptrs)  # host addresses of every shard in this process
+            stage_row = max(s.row_bytes for s in specs)
+            self.stage = [torch.empty(self.B * stage_row, dtype=torch.uint8, device=self.device)
+                          for _ in range(self.ring_depth)]
+            self.stage_iota = torch.stack([torch.arange(self.B, dtype=torch.int64) + (i << SLOT_ROW_BITS)
+                                           for i in range(self.ring_depth)]).to(self.device)
+            self.host_tables = torch.empty((self.P, self.n_max), dtype=torch.int64).pin_memory()
+            self.sources = SourceTable([t.data_ptr() for t in self.stage], self.device)
+            for s in specs:
+                self.plans.append(GatherPlan(self.sources, s.row_bytes, s.sample_bytes, s.convert,
+                                             dst_row_bytes=ring_row, variant=config.gather_variant,
+                                             max_ctas=config.gather_max_ctas, tune=config.gather_tune))
+            self.h2d_copies = 0
+        elif self.cuda:
+            if self.host_resident:
+                ptrs = [self.heap.peer_dev_ptr(g // self.P, f"shard{g % self.P}") for g in range(n_sources)]
             self.sources = SourceTable(ptrs, self.device)
             for s in specs:
                 self.plans.append(GatherPlan(self.sources, s.row_bytes, s.sample_bytes, s.convert,
@@ -223,6 +246,8 @@ class DeviceEngine:
     def alloc_window(self, k: int) -> np.ndarray:
         """Pinned host window handed to the user's post_init (reference: the MPI window)."""
         s = self.specs[k]
+        if self.host_resident and s.row_bytes == s.sample_bytes:
+            return self.shards[k].numpy(s.np_dtype, (s.nData, s.nValues))  # the window is the shard
         if self.cuda:
             buf, _ = self.heap.alloc_pinned(f"window{k}", s.nData * s.sample_bytes)
             return buf.numpy(s.np_dtype, (s.nData, s.nValues))
@@ -231,10 +256,14 @@ class DeviceEngine:
     def load_shard(self, k: int, window: np.ndarray, stream=None) -> None:
         """Copy a filled host window into the HBM shard (row stride padded to 16 bytes)."""
         s = self.specs[k]
+        if window.ctypes.data == self.shards[k].ptr:
+            return
         src = torch.from_numpy(window.reshape(s.nData, -1).view(np.uint8))
         dst = self.shards[k].tensor(torch.uint8, (s.nData, s.row_bytes))
         st = stream or self.side
-        if self.cuda:
+        if self.host_resident:
+            dst[:, :s.sample_bytes] = src
+        elif self.cuda:
             with torch.cuda.stream(st):
                 if s.row_bytes == s.sample_bytes:
                     dst.copy_(src, non_blocking=True)
@@ -343,13 +372,33 @@ class DeviceEngine:
     # -- batch assembly (fetch stream) --------------------------------------------------------------
     def gather(self, k: int, buf: int, first_row: int, ring_slot: int, n: Optional[int] = None) -> None:
         n = self.B if n is None else n
-        if self.cuda:
+        if self.stage is not None:
+            # N9 stage_host: this step's rows, pinned host -> device, then the convert kernel
+            s = self.specs[k]
+            copies = C.c_int64()
+            slots_ptr = self.host_tables.data_ptr() + (k * self.n_max + first_row) * 8
+            N.check(N.lib().bddl_stage_slots(C.c_void_p(self.stage[ring_slot].data_ptr()), s.row_bytes, self.h_bases,
+                                             len(self.h_bases), s.row_bytes, C.c_void_p(slots_ptr), n, s.row_bytes,
+                                             C.c_void_p(self.fetch.cuda_stream), C.byref(copies)))
+            self.h2d_copies += copies.value
+            self.plans[k].run_ptr(self.stage_iota[ring_slot].data_ptr(), self.ring[ring_slot].data_ptr(), n,
+                                  self.fetch.cuda_stream)
+            self.launches += 1
+        elif self.cuda:
             self.plans[k].run_ptr(self.table_ptr(k, buf, first_row), self.ring[ring_slot].data_ptr(), n,
                                   self.fetch.cuda_stream)
             self.launches += 1
         else:
             slots = self.tables[k, buf, first_row:first_row + n].numpy()
             self.plans[k].run(slots, self.ring[ring_slot])
+
+    def on_lend(self, k: int, buf: int) -> None:
+        """Called when the consumer borrows window k: host staging needs the table on the host."""
+        if self.stage is not None:
+            n = self.specs[k].nData
+            with torch.cuda.stream(self.fetch):
+                self.host_tables[k, :n].copy_(self.tables[k, buf, :n], non_blocking=True)
+            self.fetch.synchronize()
 
     def batch_views(self, k: int, ring_slot: int):
         """Typed [B, nValues] view of a ring slot, split into the sample's fields (dim=1)."""

@@ -76,6 +76,8 @@ class SymmetricHeap:
         self.local: Dict[str, Buffer] = {}
         self.peers: Dict[Tuple[int, str], Tuple[int, int]] = {}  # (rank, name) -> (ptr, nbytes)
         self._opened: List[int] = []
+        self._host_dev: Dict[Tuple[int, str], int] = {}
+        self._registered: List[int] = []
         self._attached: List[Tuple[int, int]] = []
         self._session = comm.bcast_obj(uuid.uuid4().hex[:12] if comm.rank == 0 else None, 0)
         self._closed = False
@@ -111,6 +113,29 @@ class SymmetricHeap:
         self.local[name] = buf
         return buf, int(d.value)
 
+    def alloc_host_shared(self, name: str, nbytes: int) -> Buffer:
+        """Pinned host memory every process of the node can map: POSIX shm + cudaHostRegister.
+        The buffer is published like device buffers; peers register it too, so any GPU can copy
+        from it or read it from a kernel (host-resident datasets)."""
+        nbytes = max(4096, (int(nbytes) + 4095) // 4096 * 4096)
+        lib = N.lib()
+        p = C.c_void_p()
+        shm = f"/bddl_{self._session}_{self.comm.world_rank}_h{len(self.local)}"
+        N.check(lib.bddl_shm_create(shm.encode(), nbytes, C.byref(p)))
+        buf = Buffer(name, p.value, nbytes, torch.device("cpu"), shm_name=shm)
+        buf.host_shared = True
+        buf.dev_ptr = 0
+        if self.device.type == "cuda":
+            d = C.c_void_p()
+            N.check(lib.bddl_host_register(p, nbytes, C.byref(d)))
+            buf.dev_ptr = int(d.value)
+        self.local[name] = buf
+        return buf
+
+    def peer_dev_ptr(self, rank: int, name: str) -> int:
+        """Device-visible address of a host-shared buffer (this process's mapping of it)."""
+        return self._host_dev[(rank, name)]
+
     # -- exchange -------------------------------------------------------------------------------
     def publish(self) -> None:
         """Collective: make every local buffer addressable by every peer."""
@@ -119,7 +144,10 @@ class SymmetricHeap:
         for name, b in self.local.items():
             if b._keep is not None:
                 continue  # pinned host staging is private
-            if self.device.type == "cuda":
+            if getattr(b, "host_shared", False):
+                mine[name] = ("hshm", b.shm_name, b.nbytes, b.ptr, os.getpid(), -1)
+                self._host_dev[(self.comm.rank, name)] = b.dev_ptr
+            elif self.device.type == "cuda":
                 h = (C.c_uint8 * 64)()
                 N.check(lib.bddl_ipc_get_handle(C.c_void_p(b.ptr), h))
                 mine[name] = ("ipc", bytes(h), b.nbytes, b.ptr, os.getpid(), self.device.index or 0)
@@ -130,7 +158,21 @@ class SymmetricHeap:
             for name, (kind, handle, nbytes, ptr, pid, dev) in entries.items():
                 if (r, name) in self.peers:
                     continue
-                if r == self.comm.rank or pid == os.getpid() and (kind == "shm" or dev == (self.device.index or 0)):
+                if kind == "hshm" and r != self.comm.rank:
+                    if pid == os.getpid():
+                        self.peers[(r, name)] = (ptr, nbytes)
+                        self._host_dev[(r, name)] = self._host_dev.get((r, name), 0)
+                        continue
+                    p = C.c_void_p()
+                    N.check(lib.bddl_shm_attach(handle.encode(), nbytes, C.byref(p)))
+                    self._attached.append((p.value, nbytes))
+                    self.peers[(r, name)] = (p.value, nbytes)
+                    if self.device.type == "cuda":
+                        d = C.c_void_p()
+                        N.check(lib.bddl_host_register(p, nbytes, C.byref(d)))
+                        self._registered.append(p.value)
+                        self._host_dev[(r, name)] = int(d.value)
+                elif r == self.comm.rank or pid == os.getpid() and (kind == "shm" or dev == (self.device.index or 0)):
                     self.peers[(r, name)] = (ptr, nbytes)
                 elif kind == "ipc":
                     if pid == os.getpid():
@@ -150,8 +192,8 @@ class SymmetricHeap:
                     self.peers[(r, name)] = (p.value, nbytes)
         self.comm.barrier()
         # names can go once everybody is attached; the memory lives until the last unmap
-        if self.device.type == "cpu":
-            for b in self.local.values():
+        for b in self.local.values():
+            if self.device.type == "cpu" or getattr(b, "host_shared", False):
                 if b.shm_name:
                     lib.bddl_shm_unlink(b.shm_name.encode())
                     b.shm_name = ""
@@ -175,6 +217,8 @@ class SymmetricHeap:
                 torch.cuda.synchronize(self.device)
             except Exception:
                 pass
+        for p in self._registered:
+            lib.bddl_host_unregister(C.c_void_p(p))
         for p in self._opened:
             lib.bddl_ipc_close_handle(C.c_void_p(p))
         for p, n in self._attached:
@@ -183,6 +227,12 @@ class SymmetricHeap:
             b._u8 = None
             if b._keep is not None and b._keep[0] == "pinned":
                 lib.bddl_host_free(C.c_void_p(b.ptr))
+            elif getattr(b, "host_shared", False):
+                if self.device.type == "cuda":
+                    lib.bddl_host_unregister(C.c_void_p(b.ptr))
+                if b.shm_name:
+                    lib.bddl_shm_unlink(b.shm_name.encode())
+                lib.bddl_shm_detach(C.c_void_p(b.ptr), b.nbytes)
             elif self.device.type == "cuda":
                 lib.bddl_free(C.c_void_p(b.ptr))
             else:

@@ -1,0 +1,146 @@
+"""The public API on a real GPU: batches delivered by the sm_100a kernels must be the batches the
+reference semantics prescribe (tests/oracle.py), for HBM- and host-resident shards."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import ddl_b200 as ddl
+from oracle import expected_epochs
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+class IdShard(ddl.ProducerFunctionSkeleton):
+    def __init__(self, n, v, declare):
+        super().__init__()
+        self.n, self.v, self.declare, self.rng = n, v, declare, None
+
+    def on_init(self, **kw):
+        super().on_init(**kw)
+        self.rng = np.random.default_rng(self.rank_global)
+        return ddl.DataProducerOnInitReturn(self.n, self.v, (self.n, self.v), (1, self.v - 1),
+                                            shuffle_seed=self.rank_global if self.declare else None)
+
+    def post_init(self, **kw):
+        a = kw["my_ary"]
+        self.my_ary = a
+        gid = self.rank_global * 1_000_000 + np.arange(self.n)
+        a[:, 0] = gid
+        a[:, 1:] = (gid[:, None] % 97)
+
+    def execute_function(self, **kw):
+        self.rng.shuffle(self.my_ary)
+
+
+def _run(cfg, n=3000, v=12, B=256, E=5, P=2, declare=True):
+    seen = []
+
+    @ddl.distributed_dataloader(n_instances=1, n_producers=P, config=cfg)
+    def main(env, conn):
+        assert env.device.type == "cuda"
+        loader = ddl.DistributedDataLoader(IdShard(n, v, declare), B, conn, E, 0.5, "sendrecv_replace", 0, 1)
+        for _ in range(E):
+            ids = []
+            for a, b in loader:
+                assert a.is_cuda and a.shape == (B, 1) and b.shape == (B, v - 1)
+                ids.append(a[:, 0].long().cpu().numpy())
+                assert torch.equal(b[:, 0].long().cpu(), torch.from_numpy(ids[-1] % 97))
+                loader.mark(ddl.Marker.END_OF_BATCH)
+            loader.mark(ddl.Marker.END_OF_EPOCH)
+            seen.append(np.concatenate(ids))
+
+    main()
+    exp = expected_epochs(1, P, n, B, E, 0.5)[0]
+    assert np.array_equal(np.stack(seen), exp)
+
+
+@pytest.mark.parametrize("mode,declare", [("device", True), ("trace", False), ("host", False)])
+def test_single_gpu_matches_reference_order(mode, declare):
+    _run(ddl.LoaderConfig(shuffle_mode=mode), declare=declare)
+
+
+@pytest.mark.parametrize("stage", ["memcpy", "pull"])
+def test_host_resident_shards(stage):
+    _run(ddl.LoaderConfig(residency="host", host_stage=stage), v=16)
+
+
+def test_prefetch_off_and_deep_ring():
+    _run(ddl.LoaderConfig(prefetch=False))
+    _run(ddl.LoaderConfig(ring_depth=4))
+
+
+def test_uint8_images_normalised_to_bf16():
+    n, B = 1024, 64
+    hw = 24 * 24
+    cv = ddl.Convert.normalize_u8((0.485, 0.456, 0.406), (0.229, 0.224, 0.225), hw)
+    data = np.random.default_rng(1).integers(0, 256, size=(n, 3 * hw), dtype=np.uint8)
+
+    class Img(ddl.ProducerFunctionSkeleton):
+        def on_init(self, **kw):
+            super().on_init(**kw)
+            return ddl.DataProducerOnInitReturn(n, 3 * hw, (n, 3 * hw), (3 * hw,), dtype=np.uint8, convert=cv,
+                                                shuffle_seed=5)
+
+        def post_init(self, **kw):
+            kw["my_ary"][...] = data
+
+    @ddl.distributed_dataloader(n_instances=1, n_producers=1)
+    def main(env, conn):
+        loader = ddl.DistributedDataLoader(Img(), B, conn, 1)
+        perm = np.random.default_rng(5).permutation(n) if False else None
+        order = np.arange(n)
+        np.random.default_rng(5).shuffle(order)
+        sc = torch.tensor(cv.scale).repeat_interleave(hw)
+        bi = torch.tensor(cv.bias).repeat_interleave(hw)
+        for i, (x,) in enumerate(loader):
+            ref = (torch.from_numpy(data[order[i * B:(i + 1) * B]]).float() * sc + bi).to(torch.bfloat16)
+            assert x.dtype == torch.bfloat16 and torch.equal(x.cpu().view(torch.int16), ref.view(torch.int16))
+            loader.mark(ddl.Marker.END_OF_BATCH)
+        loader.mark(ddl.Marker.END_OF_EPOCH)
+
+    main()
+
+
+def _torchrun(nproc, cfg, tmp_path, timeout=240):
+    import socket
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    cfg = dict(cfg, out=str(tmp_path))
+    env = dict(os.environ, BDDL_TEST_CFG=json.dumps(cfg))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(HERE, "workers", "run_loader.py")]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+
+
+def test_process_transport_consumer_on_gpu(tmp_path):
+    """Reference layout on one GPU: the consumer stages the borrowed host window to the device."""
+    cfg = {"n_instances": 1, "n": 4000, "v": 8, "B": 256, "epochs": 4, "fraction": 0.5, "cpu": False}
+    _torchrun(3, cfg, tmp_path)
+    exp = expected_epochs(1, 2, 4000, 256, 4, 0.5)[0]
+    assert np.array_equal(np.load(os.path.join(str(tmp_path), "seen_0.npy")), exp)
+
+
+@pytest.mark.multigpu
+@pytest.mark.parametrize("barrier", ["nccl", "flags", "host"])
+def test_two_gpus_global_shuffle_over_nvlink(tmp_path, barrier):
+    """One process per GPU: slot tables exchanged and samples pulled through peer mappings."""
+    cfg = {"n_instances": 2, "n_producers": 2, "n": 4096, "v": 32, "B": 256, "epochs": 6, "fraction": 0.5,
+           "shuffle_mode": "device", "declare_seed": True, "cpu": False}
+    env_extra = {"DDL_B200_BARRIER": barrier}
+    os.environ.update(env_extra)
+    try:
+        _torchrun(2, cfg, tmp_path)
+    finally:
+        os.environ.pop("DDL_B200_BARRIER", None)
+    exp = expected_epochs(2, 2, 4096, 256, 6, 0.5)
+    for i in range(2):
+        assert np.array_equal(np.load(os.path.join(str(tmp_path), f"seen_{i}.npy")), exp[i])
