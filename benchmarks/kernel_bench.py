@@ -113,11 +113,20 @@ def main():
     for name, cv, sb, batch, shard in cases:
         if args.only and args.only not in name:
             continue
-        combos = [(N.VARIANT_LDG, 0), (N.VARIANT_TMA, 0), (N.VARIANT_TMA, 1), (N.VARIANT_TMA, 2)]
+        combos = [(N.VARIANT_LDG, 0), (N.VARIANT_TMA, 0), (N.VARIANT_TMA, 1), (N.VARIANT_TMA, 2), (N.VARIANT_TMA, 3)]
         if args.quick:
             combos = [(N.VARIANT_LDG, 0), (N.VARIANT_TMA, 0)]
         for variant, tune in combos:
             r = bench_gather(name, cv, sb, batch, shard, variant, tune)
+            results.append(r)
+            print(json.dumps(r), flush=True)
+    if not args.only or "batch_sweep" in args.only:
+        for b in (64, 256, 1024, 4096):
+            for variant in (N.VARIANT_LDG, N.VARIANT_TMA):
+                r = bench_gather("imagenet_u8_bf16_batch_sweep", img, 150528, b, 4 << 30, variant, 0)
+                results.append(r)
+                print(json.dumps(r), flush=True)
+            r = bench_gather("imagenet_copy_batch_sweep", Convert.copy(), 150528, b, 4 << 30, N.VARIANT_TMA, 0)
             results.append(r)
             print(json.dumps(r), flush=True)
     if not args.only or "sm_budget" in args.only:

@@ -117,10 +117,48 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 // x*scale + bias with two roundings, so results match a plain fp32 PyTorch expression exactly.
 __device__ __forceinline__ float affine(float x, float sc, float bi) { return __fadd_rn(__fmul_rn(x, sc), bi); }
 
+// uint8 -> float without the conversion pipe: PRMT builds the float 2^23 + x, and
+// fma(2^23 + x, s, -(2^23 * s)) is x*s rounded once, i.e. bit-identical to fmul(float(x), s)
+// (2^23 * s is exact).  Three full-rate instructions per element: PRMT, FFMA, FADD.
+__device__ __forceinline__ float u8_magic(uint32_t word, int k) {
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440u + (uint32_t)k));
+}
+__device__ __forceinline__ float affine_u8(float magic, float sc, float noff, float bi) {
+    return __fadd_rn(__fmaf_rn(magic, sc, noff), bi);
+}
+
 template <bool CHAN>
 __device__ __forceinline__ int channel_of(const KParams& p, uint32_t e) {
     if (!CHAN) return 0;
     return (int)((e / p.chan_stride) % (uint32_t)p.n_channels);
+}
+
+// Per-chunk, warp-uniform channel context.  When a channel plane is at least one chunk long a
+// chunk touches at most two channels, so a group only compares its offset with `boundary`;
+// shorter planes fall back to a division per group.
+struct ChanCtx {
+    float sc0, bi0, no0;
+    float sc1, bi1, no1;
+    uint32_t boundary;  // chunk-relative element index where the second channel starts
+    bool fast;
+};
+
+template <bool CHAN>
+__device__ __forceinline__ ChanCtx make_ctx(const KParams& p, uint32_t elem0, uint32_t chunk_elems) {
+    ChanCtx c;
+    int c0 = 0, c1 = 0;
+    c.boundary = 0xffffffffu;
+    c.fast = true;
+    if (CHAN) {
+        const uint32_t q = elem0 / p.chan_stride;
+        c0 = (int)(q % (uint32_t)p.n_channels);
+        c1 = c0 + 1 == p.n_channels ? 0 : c0 + 1;
+        c.boundary = p.chan_stride - (elem0 - q * p.chan_stride);
+        c.fast = p.chan_stride >= chunk_elems;
+    }
+    c.sc0 = p.scale[c0], c.bi0 = p.bias[c0], c.no0 = __fmul_rn(-8388608.0f, c.sc0);
+    c.sc1 = p.scale[c1], c.bi1 = p.bias[c1], c.no1 = __fmul_rn(-8388608.0f, c.sc1);
+    return c;
 }
 
 // Source loads: G = global memory through the read-only path, otherwise shared memory.
@@ -145,9 +183,11 @@ __device__ __forceinline__ uint8_t ld1(const uint8_t* q) {
     return *q;
 }
 
-// One output vector (16 bytes) from PER input elements starting at src.
+// One output vector (16 bytes) from PER input elements starting at src.  e_rel / e_abs: index of
+// the group's first element relative to the chunk / to the sample.
 template <int MODE, bool CHAN, bool G>
-__device__ __forceinline__ uint4 convert_group(const KParams& p, const uint8_t* src, uint32_t e0) {
+__device__ __forceinline__ uint4 convert_group(const KParams& p, const ChanCtx& cx, const uint8_t* src,
+                                               uint32_t e_rel, uint32_t e_abs) {
     using C = Cvt<MODE>;
     uint4 out;
     if constexpr (MODE == BDDL_CVT_COPY) {
@@ -166,13 +206,13 @@ __device__ __forceinline__ uint4 convert_group(const KParams& p, const uint8_t* 
                 const uint2 v = ld8<G>(src);
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    f[k] = (float)((v.x >> (8 * k)) & 0xffu);
-                    f[4 + k] = (float)((v.y >> (8 * k)) & 0xffu);
+                    f[k] = u8_magic(v.x, k);
+                    f[4 + k] = u8_magic(v.y, k);
                 }
             } else {
                 const uint32_t v = ld4<G>(src);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) f[k] = (float)((v >> (8 * k)) & 0xffu);
+                for (int k = 0; k < 4; ++k) f[k] = u8_magic(v, k);
             }
         } else {
             const uint4 a = ld16<G>(src);
@@ -182,17 +222,27 @@ __device__ __forceinline__ uint4 convert_group(const KParams& p, const uint8_t* 
             f[4] = __uint_as_float(b.x), f[5] = __uint_as_float(b.y);
             f[6] = __uint_as_float(b.z), f[7] = __uint_as_float(b.w);
         }
-        const int c0 = channel_of<CHAN>(p, e0);
-        const int c1 = channel_of<CHAN>(p, e0 + C::PER - 1);
-        if (c0 == c1) {
-            const float sc = p.scale[c0], bi = p.bias[c0];
+        auto apply = [](float x, float sc, float no, float bi) {
+            if constexpr (C::IN_ES == 1) return affine_u8(x, sc, no, bi);
+            else return affine(x, sc, bi);
+        };
+        if (!CHAN || (cx.fast && (e_rel + C::PER <= cx.boundary || e_rel >= cx.boundary))) {
+            const bool second = CHAN && e_rel >= cx.boundary;
+            const float sc = second ? cx.sc1 : cx.sc0, bi = second ? cx.bi1 : cx.bi0, no = second ? cx.no1 : cx.no0;
 #pragma unroll
-            for (int k = 0; k < C::PER; ++k) f[k] = affine(f[k], sc, bi);
+            for (int k = 0; k < C::PER; ++k) f[k] = apply(f[k], sc, no, bi);
+        } else if (cx.fast) {
+#pragma unroll
+            for (int k = 0; k < C::PER; ++k) {
+                const bool second = e_rel + k >= cx.boundary;
+                f[k] = apply(f[k], second ? cx.sc1 : cx.sc0, second ? cx.no1 : cx.no0, second ? cx.bi1 : cx.bi0);
+            }
         } else {
 #pragma unroll
             for (int k = 0; k < C::PER; ++k) {
-                const int c = channel_of<CHAN>(p, e0 + k);
-                f[k] = affine(f[k], p.scale[c], p.bias[c]);
+                const int c = channel_of<CHAN>(p, e_abs + k);
+                const float sc = p.scale[c];
+                f[k] = apply(f[k], sc, __fmul_rn(-8388608.0f, sc), p.bias[c]);
             }
         }
         if constexpr (C::OUT_ES == 2) {
@@ -233,16 +283,18 @@ __device__ __forceinline__ void convert_one(const KParams& p, const uint8_t* src
 }
 
 // Convert the payload of one chunk (src: shared or global) and pad the rest of its region.
-template <int MODE, bool CHAN, bool G, int UNROLL>
+template <int MODE, bool CHAN, bool G, int UNROLL, uint32_t CHUNK_ELEMS>
 __device__ __forceinline__ void convert_chunk(const KParams& p, const uint8_t* __restrict__ src,
                                               const Item& it, int lane) {
     using C = Cvt<MODE>;
     uint8_t* __restrict__ dst = it.dst;
     const uint32_t n_elems = it.in_bytes / C::IN_ES;
     const uint32_t n_groups = n_elems / C::PER;
+    const ChanCtx cx = make_ctx<CHAN>(p, it.elem0, CHUNK_ELEMS);
 #pragma unroll UNROLL
     for (uint32_t g = lane; g < n_groups; g += 32) {
-        const uint4 v = convert_group<MODE, CHAN, G>(p, src + (size_t)g * (C::PER * C::IN_ES), it.elem0 + g * C::PER);
+        const uint4 v = convert_group<MODE, CHAN, G>(p, cx, src + (size_t)g * (C::PER * C::IN_ES), g * C::PER,
+                                                     it.elem0 + g * C::PER);
         *reinterpret_cast<uint4*>(dst + (size_t)g * 16) = v;
     }
     const uint32_t done = n_groups * C::PER;
@@ -271,18 +323,18 @@ __global__ void __launch_bounds__(kWarps * 32) gather_ldg_kernel(const __grid_co
     const uint32_t nw = gridDim.x * kWarps;
     for (uint32_t item = gw; item < p.n_items; item += nw) {
         const Item it = resolve_item<MODE, CHUNK>(p, item);
-        convert_chunk<MODE, CHAN, true, 4>(p, it.src, it, lane);
+        convert_chunk<MODE, CHAN, true, 4, CHUNK / Cvt<MODE>::IN_ES>(p, it.src, it, lane);
     }
 }
 
 // ---- TMA / convert form ------------------------------------------------------------------------
-template <int MODE, bool CHAN, int CHUNK, int STAGES>
-__global__ void __launch_bounds__(kWarps * 32) gather_tma_cvt_kernel(const __grid_constant__ KParams p) {
+template <int MODE, bool CHAN, int CHUNK, int STAGES, int NW>
+__global__ void __launch_bounds__(NW * 32) gather_tma_cvt_kernel(const __grid_constant__ KParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     uint8_t* ring = smem + (size_t)warp * STAGES * CHUNK;
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)kWarps * STAGES * CHUNK) + warp * STAGES;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)NW * STAGES * CHUNK) + warp * STAGES;
 
     if (lane == 0) {
 #pragma unroll
@@ -291,8 +343,8 @@ __global__ void __launch_bounds__(kWarps * 32) gather_tma_cvt_kernel(const __gri
     }
     __syncwarp();
 
-    const uint32_t gw = blockIdx.x * kWarps + warp;
-    const uint32_t nw = gridDim.x * kWarps;
+    const uint32_t gw = blockIdx.x * NW + warp;
+    const uint32_t nw = gridDim.x * NW;
     const uint32_t n_my = gw < p.n_items ? (p.n_items - gw + nw - 1) / nw : 0;
 
     auto issue = [&](uint32_t k) {
@@ -315,7 +367,7 @@ __global__ void __launch_bounds__(kWarps * 32) gather_tma_cvt_kernel(const __gri
             mbar_wait(full + s, (phase >> s) & 1u);
             phase ^= 1u << s;
         }
-        convert_chunk<MODE, CHAN, false, 2>(p, ring + (size_t)s * CHUNK, it, lane);
+        convert_chunk<MODE, CHAN, false, 2, CHUNK / Cvt<MODE>::IN_ES>(p, ring + (size_t)s * CHUNK, it, lane);
         __syncwarp();
         if (lane == 0 && k + STAGES < n_my) {
             fence_proxy_async_smem();  // the warp's reads of this stage precede the next bulk write
@@ -387,12 +439,12 @@ uint32_t chunks_for(int64_t sample_bytes) {
     return (uint32_t)((sample_bytes + CHUNK - 1) / CHUNK);
 }
 
-int grid_for(const bddl_gather_desc* d, uint32_t n_items, int* grid) {
+int grid_for(const bddl_gather_desc* d, uint32_t n_items, int* grid, int warps = kWarps) {
     int sms = 0;
     int rc = sm_count(&sms);
     if (rc) return rc;
     int cap = d->max_ctas > 0 ? d->max_ctas : sms;
-    int need = (int)((n_items + kWarps - 1) / kWarps);
+    int need = (int)((n_items + warps - 1) / warps);
     *grid = need < cap ? need : cap;
     if (*grid < 1) *grid = 1;
     return 0;
@@ -420,13 +472,14 @@ int launch_ldg(const bddl_gather_desc* d, KParams& p, cudaStream_t st) {
     return 0;
 }
 
-template <int MODE, bool CHAN, int CHUNK, int STAGES>
+template <int MODE, bool CHAN, int CHUNK, int STAGES, int NW>
 int launch_tma_cvt(const bddl_gather_desc* d, KParams& p, cudaStream_t st) {
-    constexpr size_t smem = (size_t)kWarps * STAGES * CHUNK + (size_t)kWarps * STAGES * sizeof(uint64_t);
+    constexpr size_t smem = (size_t)NW * STAGES * CHUNK + (size_t)NW * STAGES * sizeof(uint64_t);
+    static_assert(smem <= 227 * 1024, "stage rings exceed shared memory");
     static bool configured[64];
     int dev = 0;
     BDDL_CUDA(cudaGetDevice(&dev));
-    auto kernel = gather_tma_cvt_kernel<MODE, CHAN, CHUNK, STAGES>;
+    auto kernel = gather_tma_cvt_kernel<MODE, CHAN, CHUNK, STAGES, NW>;
     if (!configured[dev & 63]) {
         int rc = set_smem(kernel, smem);
         if (rc) return rc;
@@ -435,9 +488,9 @@ int launch_tma_cvt(const bddl_gather_desc* d, KParams& p, cudaStream_t st) {
     p.chunks_per_sample = chunks_for<CHUNK>(d->sample_bytes);
     p.n_items = (uint32_t)d->n_samples * p.chunks_per_sample;
     int grid = 0;
-    int rc = grid_for(d, p.n_items, &grid);
+    int rc = grid_for(d, p.n_items, &grid, NW);
     if (rc) return rc;
-    kernel<<<grid, kWarps * 32, smem, st>>>(p);
+    kernel<<<grid, NW * 32, smem, st>>>(p);
     bddl_count_launch(1);
     BDDL_CUDA(cudaGetLastError());
     return 0;
@@ -471,11 +524,13 @@ int launch_mode(const bddl_gather_desc* d, KParams& p, bool tma, cudaStream_t st
     if (!tma) return launch_ldg<MODE, CHAN>(d, p, st);
     switch (d->tune) {
         case 1:
-            return launch_tma_cvt<MODE, CHAN, 4096, 6>(d, p, st);
+            return launch_tma_cvt<MODE, CHAN, 2048, 6, 16>(d, p, st);
         case 2:
-            return launch_tma_cvt<MODE, CHAN, 2048, 12>(d, p, st);
+            return launch_tma_cvt<MODE, CHAN, 8192, 3, 8>(d, p, st);
+        case 3:
+            return launch_tma_cvt<MODE, CHAN, 2048, 3, 32>(d, p, st);
         default:
-            return launch_tma_cvt<MODE, CHAN, 8192, 3>(d, p, st);
+            return launch_tma_cvt<MODE, CHAN, 4096, 3, 16>(d, p, st);
     }
 }
 

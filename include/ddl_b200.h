@@ -110,7 +110,7 @@ typedef struct bddl_gather_desc {
     uint32_t pad_bits;               /* variable-size: output element used for padding            */
     int32_t variant;                 /* BDDL_VARIANT_*                                            */
     int32_t max_ctas;                /* SM budget; 0 = one CTA per SM                             */
-    int32_t tune;                    /* 0 = 8 KiB x 3 stages, 1 = 4 KiB x 6, 2 = 2 KiB x 12 per warp  */
+    int32_t tune;                    /* stage ring per warp; convert: 0 = 16 warps x 3 x 4 KiB, 1 = 16 x 6 x 2 KiB, 2 = 8 x 3 x 8 KiB, 3 = 32 x 3 x 2 KiB */
 } bddl_gather_desc;
 
 int bddl_exchange_gather_collate(const bddl_gather_desc* desc, void* stream);

@@ -132,7 +132,7 @@ def _convert(mode, sample_bytes, channels):
 
 @pytest.mark.parametrize("mode,sample_bytes,dtype,channels", CASES)
 @pytest.mark.parametrize("variant,tune", [(N.VARIANT_LDG, 0), (N.VARIANT_TMA, 0), (N.VARIANT_TMA, 1),
-                                          (N.VARIANT_TMA, 2), (N.VARIANT_AUTO, 0)])
+                                          (N.VARIANT_TMA, 2), (N.VARIANT_TMA, 3), (N.VARIANT_AUTO, 0)])
 def test_gather_matches_reference(mode, sample_bytes, dtype, channels, variant, tune):
     n_sources, rows, n = 3, 64, 97
     shards, row_bytes = _shards(n_sources, rows, sample_bytes, dtype=dtype)
