@@ -14,7 +14,11 @@
 //     (__match_any_sync), so they are applied as 32 parallel swaps;
 //   * any batch that is ambiguous, collides, crosses a power-of-two mask boundary or reaches
 //     the end of the table replays its 32 draws one at a time (exact sequential semantics).
-// Table accesses go through L2 (ld/st .cg) so that lanes always see each other's swaps.
+// Table accesses go through L2 (ld/st .cg) so that lanes always see each other's swaps.  Once
+// the running index drops below kSmemEntries the live prefix of the table is pulled into shared
+// memory and finished there: small indices are where batches fall back to the sequential replay
+// (the ambiguous band is a large share of the range), and a replay step then costs a
+// shared-memory round trip instead of an L2 one.
 // The kernel is latency-bound by construction and is meant to run one iteration ahead on a
 // side stream, off the batch-delivery critical path.
 #include <cuda_runtime.h>
@@ -26,6 +30,8 @@
 
 namespace {
 
+constexpr int kSmemEntries = 24576;  // 192 KiB of slot ids
+
 __device__ __forceinline__ U128 shfl_u128(U128 v, int src) {
     U128 r;
     r.lo = __shfl_sync(0xffffffffu, v.lo, src);
@@ -35,8 +41,19 @@ __device__ __forceinline__ U128 shfl_u128(U128 v, int src) {
 
 __global__ void __launch_bounds__(32) perm_gen_kernel(uint64_t* tables, int64_t table_stride, int64_t n,
                                                       BddlRng* states) {
+    extern __shared__ uint64_t smem_tbl[];
     const int lane = threadIdx.x;
-    uint64_t* tbl = tables + (int64_t)blockIdx.x * table_stride;
+    uint64_t* const gtbl = tables + (int64_t)blockIdx.x * table_stride;
+    uint64_t* tbl = gtbl;
+    bool in_smem = false;
+    int64_t cached = 0;
+    auto ld = [&](int64_t x) -> uint64_t { return in_smem ? tbl[x] : __ldcg(tbl + x); };
+    auto st_ = [&](int64_t x, uint64_t v) {
+        if (in_smem)
+            tbl[x] = v;
+        else
+            __stcg(tbl + x, v);
+    };
     BddlRng* gst = states + blockIdx.x;
 
     // Warp-uniform copy of the generator.
@@ -56,9 +73,9 @@ __global__ void __launch_bounds__(32) perm_gen_kernel(uint64_t* tables, int64_t 
         draws++;
         if (v <= (uint64_t)i) {
             if (lane == 0) {
-                uint64_t a = __ldcg(tbl + i), b = __ldcg(tbl + v);
-                __stcg(tbl + i, b);
-                __stcg(tbl + v, a);
+                uint64_t a = ld(i), b = ld((int64_t)v);
+                st_(i, b);
+                st_((int64_t)v, a);
             }
             __syncwarp();
             --i;
@@ -74,6 +91,13 @@ __global__ void __launch_bounds__(32) perm_gen_kernel(uint64_t* tables, int64_t 
         U128 st = u128_add(u128_mul(lm, base), lp);
 
         while (i >= 1) {
+            if (!in_smem && i < kSmemEntries) {
+                cached = i + 1;  // entries [0, i] are all that can still change
+                for (int64_t x = lane; x < cached; x += 32) smem_tbl[x] = __ldcg(gtbl + x);
+                __syncwarp();
+                tbl = smem_tbl;
+                in_smem = true;
+            }
             const uint64_t out = pcg_output(st);
             const uint32_t d = (lane & 1) ? (uint32_t)(out >> 32) : (uint32_t)out;
             const uint64_t mask = bddl_mask_for((uint64_t)i);
@@ -97,9 +121,9 @@ __global__ void __launch_bounds__(32) perm_gen_kernel(uint64_t* tables, int64_t 
                 if (fast) {
                     if (accept) {
                         const int64_t my_i = i - (int64_t)__popc(acc & ((1u << lane) - 1u));
-                        const uint64_t a = __ldcg(tbl + my_i), b = __ldcg(tbl + v);
-                        __stcg(tbl + my_i, b);
-                        __stcg(tbl + v, a);
+                        const uint64_t a = ld(my_i), b = ld((int64_t)v);
+                        st_(my_i, b);
+                        st_((int64_t)v, a);
                     }
                     __syncwarp();
                     i -= (int64_t)__popc(acc);
@@ -118,9 +142,9 @@ __global__ void __launch_bounds__(32) perm_gen_kernel(uint64_t* tables, int64_t 
                 used = t + 1;
                 if (vt <= (uint64_t)i) {
                     if (lane == 0) {
-                        const uint64_t a = __ldcg(tbl + i), b = __ldcg(tbl + vt);
-                        __stcg(tbl + i, b);
-                        __stcg(tbl + vt, a);
+                        const uint64_t a = ld(i), b = ld((int64_t)vt);
+                        st_(i, b);
+                        st_((int64_t)vt, a);
                     }
                     __syncwarp();
                     --i;
@@ -142,6 +166,10 @@ __global__ void __launch_bounds__(32) perm_gen_kernel(uint64_t* tables, int64_t 
         }
     }
 
+    if (in_smem) {
+        __syncwarp();
+        for (int64_t x = lane; x < cached; x += 32) gtbl[x] = smem_tbl[x];
+    }
     if (lane == 0) {
         gst->state_lo = base.lo;
         gst->state_hi = base.hi;
@@ -159,7 +187,15 @@ extern "C" int bddl_perm_gen(uint64_t* d_tables, int64_t table_stride, int64_t n
         return bddl_fail(BDDL_ERR_INVALID, "perm_gen: bad arguments (n=%lld tables=%d stride=%lld)",
                          (long long)n, n_tables, (long long)table_stride);
     if (n >= (1LL << 32)) return bddl_fail(BDDL_ERR_UNSUPPORTED, "perm_gen: tables beyond 2^32 entries");
-    perm_gen_kernel<<<n_tables, 32, 0, (cudaStream_t)stream>>>(d_tables, table_stride, n, (BddlRng*)d_states);
+    constexpr size_t smem = (size_t)kSmemEntries * sizeof(uint64_t);
+    static bool configured[64];
+    int dev = 0;
+    BDDL_CUDA(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        BDDL_CUDA(cudaFuncSetAttribute(perm_gen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[dev & 63] = true;
+    }
+    perm_gen_kernel<<<n_tables, 32, smem, (cudaStream_t)stream>>>(d_tables, table_stride, n, (BddlRng*)d_states);
     bddl_count_launch(1);
     BDDL_CUDA(cudaGetLastError());
     return 0;
