@@ -188,14 +188,15 @@ def run_ours(args) -> dict:
             result.update(e2e_ms=ms, e2e_steps=steps)
 
         cfg2 = ddl.LoaderConfig.from_env(metrics=False, ring_depth=args.ring, residency="host",
-                                         host_stage=args.host_stage)
+                                         host_stage=args.host_stage, host_threads=args.host_threads, gather_variant=args.e2e_variant,
+                                         gather_tune=args.e2e_tune)
         ddl.distributed_dataloader(body_e2e, n_instances="world", n_producers=1, config=cfg2)()
         v = args.gpus * args.batch * result["e2e_steps"] / (result["e2e_ms"] * 1e-3)
         e2e = {"value": round(v, 1), "unit": "samples/s", "h2d_bytes_per_step": args.batch * SAMPLE,
                "d2h_bytes_per_step": 4, "steps": result["e2e_steps"],
-               "path": ("pinned host shard -> cudaMemcpyAsync staging -> convert kernel -> checksum D2H"
-                        if args.host_stage == "memcpy" else
-                        "pinned host shard -> kernel pulls rows over PCIe (zero-copy) + convert -> checksum D2H")}
+               "path": {"gather": "pinned host shard -> threaded CPU gather -> one cudaMemcpyAsync per step -> convert kernel -> checksum D2H",
+                        "memcpy": "pinned host shard -> cudaMemcpyAsync per row -> convert kernel -> checksum D2H",
+                        "pull": "pinned host shard -> kernel pulls rows over PCIe (zero-copy) + convert -> checksum D2H"}[args.host_stage]}
 
     if result.get("rank", 0) != 0:
         return {}
@@ -229,7 +230,10 @@ def main():
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--tune", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--host-stage", default="memcpy", choices=["memcpy", "pull"])
+    ap.add_argument("--e2e-variant", type=int, default=0)
+    ap.add_argument("--e2e-tune", type=int, default=0)
+    ap.add_argument("--host-threads", type=int, default=4)
+    ap.add_argument("--host-stage", default="gather", choices=["gather", "memcpy", "pull"])
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

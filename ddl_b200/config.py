@@ -31,7 +31,10 @@ class LoaderConfig:
     exchange: str = "pull"         # pull | push
     host_pull: bool = False        # process transport: kernel reads the pinned window directly
     residency: str = "hbm"         # device transport: shards in "hbm" or in pinned "host" memory
-    host_stage: str = "memcpy"     # host residency: "memcpy" (cudaMemcpyAsync staging) or "pull" (zero-copy)
+    # host residency: "gather" (threaded CPU gather into a pinned buffer + one cudaMemcpyAsync),
+    # "memcpy" (one cudaMemcpyAsync per row run) or "pull" (kernel reads host memory, zero-copy)
+    host_stage: str = "gather"
+    host_threads: int = 4
     timeout_s: float = 600.0       # bounded waits: a dead producer raises instead of hanging
     metrics: bool = True
     trace: bool = False            # CUDA-event timing of every loader stage
@@ -66,7 +69,7 @@ class LoaderConfig:
             raise ValueError(f"unknown barrier {self.barrier!r}")
         if self.exchange not in ("pull", "push"):
             raise ValueError(f"unknown exchange {self.exchange!r}")
-        if self.residency not in ("hbm", "host") or self.host_stage not in ("memcpy", "pull"):
-            raise ValueError("residency is 'hbm' or 'host'; host_stage is 'memcpy' or 'pull'")
+        if self.residency not in ("hbm", "host") or self.host_stage not in ("gather", "memcpy", "pull"):
+            raise ValueError("residency is 'hbm' or 'host'; host_stage is 'gather', 'memcpy' or 'pull'")
         if self.ring_depth < 2:
             raise ValueError("ring_depth must be at least 2")

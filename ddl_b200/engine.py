@@ -197,7 +197,7 @@ class DeviceEngine:
         ptrs = [self.heap.peer_ptr(g // self.P, f"shard{g % self.P}") for g in range(n_sources)]
         self.plans: List = []
         self.stage = None
-        if self.host_resident and config.host_stage == "memcpy":
+        if self.host_resident and config.host_stage in ("memcpy", "gather"):
             self.h_bases = (C.c_void_p * n_sources)(*ptrs)  # host addresses of every shard in this process
             stage_row = max(s.row_bytes for s in specs)
             self.stage = [torch.empty(self.B * stage_row, dtype=torch.uint8, device=self.device)
@@ -211,6 +211,11 @@ class DeviceEngine:
                                              dst_row_bytes=ring_row, variant=config.gather_variant,
                                              max_ctas=config.gather_max_ctas, tune=config.gather_tune))
             self.h2d_copies = 0
+            self.pinned = None
+            if config.host_stage == "gather":
+                self.pinned = [torch.empty(self.B * stage_row, dtype=torch.uint8).pin_memory()
+                               for _ in range(self.ring_depth)]
+                self.pinned_done = [None] * self.ring_depth
         elif self.cuda:
             if self.host_resident:
                 ptrs = [self.heap.peer_dev_ptr(g // self.P, f"shard{g % self.P}") for g in range(n_sources)]
@@ -377,7 +382,23 @@ class DeviceEngine:
             s = self.specs[k]
             copies = C.c_int64()
             slots_ptr = self.host_tables.data_ptr() + (k * self.n_max + first_row) * 8
-            N.check(N.lib().bddl_stage_slots(C.c_void_p(self.stage[ring_slot].data_ptr()), s.row_bytes, self.h_bases,
+            lib = N.lib()
+            if self.pinned is not None:
+                ev = self.pinned_done[ring_slot]
+                if ev is not None:
+                    ev.synchronize()  # the previous transfer out of this pinned buffer has finished
+                N.check(lib.bddl_host_gather_slots(C.c_void_p(self.pinned[ring_slot].data_ptr()), s.row_bytes,
+                                                   self.h_bases, len(self.h_bases), s.row_bytes, C.c_void_p(slots_ptr),
+                                                   n, s.row_bytes, self.cfg.host_threads))
+                N.check(lib.bddl_memcpy_async(C.c_void_p(self.stage[ring_slot].data_ptr()),
+                                              C.c_void_p(self.pinned[ring_slot].data_ptr()), n * s.row_bytes, 1,
+                                              C.c_void_p(self.fetch.cuda_stream)))
+                if ev is None:
+                    ev = self.pinned_done[ring_slot] = torch.cuda.Event()
+                ev.record(self.fetch)
+                copies.value = 1
+            else:
+                N.check(lib.bddl_stage_slots(C.c_void_p(self.stage[ring_slot].data_ptr()), s.row_bytes, self.h_bases,
                                              len(self.h_bases), s.row_bytes, C.c_void_p(slots_ptr), n, s.row_bytes,
                                              C.c_void_p(self.fetch.cuda_stream), C.byref(copies)))
             self.h2d_copies += copies.value

@@ -65,7 +65,7 @@ def test_single_gpu_matches_reference_order(mode, declare):
     _run(ddl.LoaderConfig(shuffle_mode=mode), declare=declare)
 
 
-@pytest.mark.parametrize("stage", ["memcpy", "pull"])
+@pytest.mark.parametrize("stage", ["gather", "memcpy", "pull"])
 def test_host_resident_shards(stage):
     _run(ddl.LoaderConfig(residency="host", host_stage=stage), v=16)
 
