@@ -1,0 +1,88 @@
+"""`bench.py --impl reference`: the reference arm of the headline benchmark.
+
+Runs the UNMODIFIED reference package (baseline/_ref/ddl, installed by
+baseline/install_reference.py) through its own public API and stock code path on the same
+metric and config as ddl_b200's arm: ImageNet-shaped uint8 3x224x224 samples (stored as float32
+rows by byte reinterpretation, which the reference needs), batch 256 per GPU, one instance per
+GPU, three producer processes per instance as in the reference's own test
+(reference tests/test_ddl.py:14: mpirun -np 4).  The reference delivers CPU tensors; the consumer
+copies each batch to its GPU and normalises it there, which is what its users must do
+(reference tests/run_ddl.py:233-235).
+
+No MPI exists on this image, so the reference's Python runs over the baseline-only mpi4py
+stand-in (baseline/mpi_standin) -- every number is labelled accordingly.  As wired, the
+reference never runs its global shuffle; that unmodified behaviour is the
+headline, and the run with the harness-side wiring fix is reported beside it.
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+import tempfile
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+import mpirun  # noqa: E402
+
+SAMPLE = 3 * 224 * 224
+
+
+def _one_run(n_inst, producers, rows, batch, steps, warmup, e2e, wiring_fix, fraction, timeout=1500):
+    out = tempfile.mkdtemp(prefix="bddl_ref_")
+    bpw = rows // batch
+    total = steps + warmup + 1
+    epochs = (total + bpw - 1) // bpw
+    cfg = {"mode": "bench", "fill": "bytes", "n": rows, "v": SAMPLE // 4, "B": batch, "epochs": epochs, "steps": steps,
+           "warmup": warmup, "e2e": e2e, "wiring_fix": wiring_fix, "fraction": fraction, "out": out}
+    env = {"BDDL_REF_CFG": json.dumps(cfg), "SLURM_JOBID": "1", "SLURM_GPUS_PER_NODE": str(n_inst),
+           "SLURM_NNODES": "1", "OMP_NUM_THREADS": "2"}
+    rc = mpirun.launch(n_inst * (producers + 1), [os.path.join(HERE, "ref_worker.py")], extra_env=env,
+                       timeout=timeout, quiet=True)
+    if rc != 0:
+        return None, f"reference run exited with {rc}"
+    res = []
+    for i in range(n_inst):
+        with open(os.path.join(out, f"ref_bench_{i}.json")) as fh:
+            res.append(json.load(fh))
+    ms = max(max(r["ms_device"], r["ms_wall"]) if e2e else r["ms_device"] for r in res)
+    return ms, None
+
+
+def run_reference(args) -> dict:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return {}  # the reference world is started by rank 0 alone; the other launcher ranks idle
+    if not os.path.isdir(os.path.join(HERE, "_ref", "ddl")):
+        return {"impl": "reference", "unavailable": "baseline/_ref/ddl missing: run python baseline/install_reference.py"}
+    n = args.gpus
+    cores = os.cpu_count() or 8
+    producers = max(1, min(3, cores // max(1, n) - 1))
+    rows = min(args.rows, 4096)
+    steps = min(args.steps, 96)
+    warmup = max(3, min(args.warmup, 16))
+    ms, err = _one_run(n, producers, rows, args.batch, steps, warmup, False, False, args.fraction)
+    if err:
+        return {"impl": "reference", "unavailable": err}
+    value = n * args.batch * steps / (ms * 1e-3)
+    ms_e, err_e = _one_run(n, producers, rows, args.batch, steps, warmup, True, False, args.fraction)
+    ms_w, err_w = _one_run(n, producers, rows, args.batch, steps, warmup, False, True, args.fraction)
+    return {
+        "metric": "gpu_delivered_samples_per_s", "value": round(value, 1), "unit": "samples/s", "n_gpus": n,
+        "steps": steps, "warmup": warmup, "ms_per_step": round(ms / steps, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "reference",
+        "config": {"model": "imagenet_u8_3x224x224_loader", "global_batch": args.batch * n, "seq_len": SAMPLE,
+                   "parallelism": f"dp{n}", "per_gpu_batch": args.batch, "rows_per_window": rows,
+                   "producers_per_instance": producers, "fraction_exchange": args.fraction,
+                   "global_shuffle": "as wired (never runs in the unmodified reference)",
+                   "mpi": "reference code over in-box MPI stand-in (no MPI library on image)",
+                   "adaptation": "uint8 samples stored as float32 rows by byte reinterpretation; consumer does "
+                                 ".view(uint8).to(device) + normalise + bf16 cast",
+                   "l2": "inputs larger than L2 (host windows, every row read once per epoch)"},
+        "e2e": None if err_e else {"value": round(n * args.batch * steps / (ms_e * 1e-3), 1), "unit": "samples/s",
+                                   "h2d_bytes_per_step": args.batch * SAMPLE, "d2h_bytes_per_step": 4},
+        "with_wiring_fix": None if err_w else {"value": round(n * args.batch * steps / (ms_w * 1e-3), 1),
+                                               "unit": "samples/s",
+                                               "note": "harness-side fix so the reference's global shuffle runs"},
+        "gpu_launches": None,
+    }
