@@ -233,7 +233,7 @@ def main():
     ap.add_argument("--e2e-variant", type=int, default=0)
     ap.add_argument("--e2e-tune", type=int, default=0)
     ap.add_argument("--host-threads", type=int, default=4)
-    ap.add_argument("--host-stage", default="gather", choices=["gather", "memcpy", "pull"])
+    ap.add_argument("--host-stage", default="pull", choices=["gather", "memcpy", "pull"])
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

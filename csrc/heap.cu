@@ -11,6 +11,9 @@
 #include <cuda_runtime.h>
 #include <string.h>
 
+#include <thread>
+#include <vector>
+
 #include "../include/ddl_b200.h"
 #include "common.h"
 #include "launch_count.h"
@@ -187,6 +190,70 @@ int bddl_stage_slots(void* d_dst, int64_t dst_row_bytes, const void* const* h_ba
         i = j;
     }
     if (n_copies) *n_copies = copies;
+    return 0;
+}
+
+// Multi-threaded form: the per-copy driver cost (several microseconds) is what limits a single
+// issuing thread, so n_threads host threads issue the row copies on private streams that are
+// forked from and joined back into `stream` with events.  PCIe then runs near its DMA rate.
+int bddl_stage_slots_mt(void* d_dst, int64_t dst_row_bytes, const void* const* h_bases, int32_t n_sources,
+                        int64_t row_bytes, const uint64_t* slots, int64_t n, int64_t copy_bytes, void* stream,
+                        int32_t n_threads) {
+    if (!d_dst || !h_bases || (!slots && n > 0) || copy_bytes > row_bytes || copy_bytes > dst_row_bytes)
+        return bddl_fail(BDDL_ERR_INVALID, "stage_slots_mt: bad arguments");
+    if (n_threads < 1) n_threads = 1;
+    if (n_threads > 16) n_threads = 16;
+    struct Lanes {
+        int dev = -1;
+        std::vector<cudaStream_t> streams;
+        std::vector<cudaEvent_t> done;
+        cudaEvent_t fork = nullptr;
+    };
+    static thread_local Lanes lanes;
+    int dev = 0;
+    BDDL_CUDA(cudaGetDevice(&dev));
+    if (lanes.dev != dev || (int)lanes.streams.size() < n_threads) {
+        lanes.dev = dev;
+        if (!lanes.fork) BDDL_CUDA(cudaEventCreateWithFlags(&lanes.fork, cudaEventDisableTiming));
+        while ((int)lanes.streams.size() < n_threads) {
+            cudaStream_t st;
+            cudaEvent_t ev;
+            BDDL_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+            BDDL_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+            lanes.streams.push_back(st);
+            lanes.done.push_back(ev);
+        }
+    }
+    const uint64_t row_mask = (1ULL << BDDL_SLOT_ROW_BITS) - 1;
+    for (int64_t i = 0; i < n; ++i)
+        if ((int64_t)(slots[i] >> BDDL_SLOT_ROW_BITS) >= n_sources)
+            return bddl_fail(BDDL_ERR_INVALID, "stage_slots_mt: source out of range");
+    cudaStream_t main = (cudaStream_t)stream;
+    BDDL_CUDA(cudaEventRecord(lanes.fork, main));
+    std::vector<int> rc((size_t)n_threads, 0);
+    std::vector<std::thread> th;
+    Lanes* const L = &lanes;  // thread_local: workers must use the caller's instance
+    for (int t = 0; t < n_threads; ++t) {
+        th.emplace_back([&, t] {
+            cudaSetDevice(dev);
+            cudaStream_t ws = L->streams[t];
+            cudaError_t e = cudaStreamWaitEvent(ws, L->fork, 0);
+            const int64_t i0 = n * t / n_threads, i1 = n * (t + 1) / n_threads;
+            for (int64_t i = i0; i < i1 && e == cudaSuccess; ++i) {
+                const char* from = (const char*)h_bases[slots[i] >> BDDL_SLOT_ROW_BITS] +
+                                   (int64_t)(slots[i] & row_mask) * row_bytes;
+                e = cudaMemcpyAsync((char*)d_dst + i * dst_row_bytes, from, (size_t)copy_bytes,
+                                    cudaMemcpyHostToDevice, ws);
+            }
+            if (e == cudaSuccess) e = cudaEventRecord(L->done[t], ws);
+            rc[t] = (int)e;
+        });
+    }
+    for (auto& x : th) x.join();
+    for (int t = 0; t < n_threads; ++t) {
+        if (rc[t]) return bddl_fail(rc[t], "stage_slots_mt: worker %d failed: %s", t, cudaGetErrorString((cudaError_t)rc[t]));
+        BDDL_CUDA(cudaStreamWaitEvent(main, lanes.done[t], 0));
+    }
     return 0;
 }
 

@@ -23,6 +23,9 @@ class LoaderConfig:
     #   "host"   -> run execute_function on the real pinned window and re-upload it
     shuffle_mode: str = "auto"
     ring_depth: int = 2            # batch buffers in flight (double buffering)
+    # CUDA priority of the batch-assembly stream.  Equal priority (0) by default: a high-priority
+    # all-SM gather was measured to hold back small kernels of the training stream until it ended.
+    fetch_priority: int = 0
     prefetch: bool = True          # launch batch i+1 while batch i is being consumed
     barrier: str = "auto"          # cross-rank stream barrier: auto | nccl | flags | host
     gather_variant: int = 0        # BDDL_VARIANT_*
@@ -33,7 +36,7 @@ class LoaderConfig:
     residency: str = "hbm"         # device transport: shards in "hbm" or in pinned "host" memory
     # host residency: "gather" (threaded CPU gather into a pinned buffer + one cudaMemcpyAsync),
     # "memcpy" (one cudaMemcpyAsync per row run) or "pull" (kernel reads host memory, zero-copy)
-    host_stage: str = "gather"
+    host_stage: str = "pull"
     host_threads: int = 4
     timeout_s: float = 600.0       # bounded waits: a dead producer raises instead of hanging
     metrics: bool = True

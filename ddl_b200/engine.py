@@ -188,7 +188,7 @@ class DeviceEngine:
         if self.cuda:
             self.main = torch.cuda.current_stream(self.device)
             self.side = torch.cuda.Stream(self.device, priority=0)      # table production
-            self.fetch = torch.cuda.Stream(self.device, priority=-1)    # batch assembly
+            self.fetch = torch.cuda.Stream(self.device, priority=config.fetch_priority)  # batch assembly
         else:
             self.main = self.side = self.fetch = NullStream()
 
@@ -397,6 +397,12 @@ class DeviceEngine:
                     ev = self.pinned_done[ring_slot] = torch.cuda.Event()
                 ev.record(self.fetch)
                 copies.value = 1
+            elif self.cfg.host_threads > 1:
+                N.check(lib.bddl_stage_slots_mt(C.c_void_p(self.stage[ring_slot].data_ptr()), s.row_bytes,
+                                                self.h_bases, len(self.h_bases), s.row_bytes, C.c_void_p(slots_ptr),
+                                                n, s.row_bytes, C.c_void_p(self.fetch.cuda_stream),
+                                                self.cfg.host_threads))
+                copies.value = n
             else:
                 N.check(lib.bddl_stage_slots(C.c_void_p(self.stage[ring_slot].data_ptr()), s.row_bytes, self.h_bases,
                                              len(self.h_bases), s.row_bytes, C.c_void_p(slots_ptr), n, s.row_bytes,

@@ -148,6 +148,9 @@ int bddl_stage_slots(void* d_dst, int64_t dst_row_bytes, const void* const* h_ba
                      int64_t row_bytes, const uint64_t* slots, int64_t n, int64_t copy_bytes, void* stream,
                      int64_t* n_copies);
 
+int bddl_stage_slots_mt(void* d_dst, int64_t dst_row_bytes, const void* const* h_bases, int32_t n_sources,
+                        int64_t row_bytes, const uint64_t* slots, int64_t n, int64_t copy_bytes, void* stream,
+                        int32_t n_threads);
 /* CPU half of stage_host: gather a batch's rows from pinned shards into one contiguous pinned
  * buffer with a persistent thread pool (then a single cudaMemcpyAsync moves it). */
 int bddl_host_gather_slots(void* h_dst, int64_t dst_row_bytes, const void* const* h_bases, int32_t n_sources,
