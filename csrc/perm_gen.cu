@@ -187,12 +187,14 @@ extern "C" int bddl_perm_gen(uint64_t* d_tables, int64_t table_stride, int64_t n
         return bddl_fail(BDDL_ERR_INVALID, "perm_gen: bad arguments (n=%lld tables=%d stride=%lld)",
                          (long long)n, n_tables, (long long)table_stride);
     if (n >= (1LL << 32)) return bddl_fail(BDDL_ERR_UNSUPPORTED, "perm_gen: tables beyond 2^32 entries");
-    constexpr size_t smem = (size_t)kSmemEntries * sizeof(uint64_t);
+    constexpr size_t smem_max = (size_t)kSmemEntries * sizeof(uint64_t);
+    // only as much shared memory as the table can use, so that small tables co-reside with other kernels
+    const size_t smem = (size_t)(n < kSmemEntries ? (n > 0 ? n : 1) : kSmemEntries) * sizeof(uint64_t);
     static bool configured[64];
     int dev = 0;
     BDDL_CUDA(cudaGetDevice(&dev));
     if (!configured[dev & 63]) {
-        BDDL_CUDA(cudaFuncSetAttribute(perm_gen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        BDDL_CUDA(cudaFuncSetAttribute(perm_gen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
         configured[dev & 63] = true;
     }
     perm_gen_kernel<<<n_tables, 32, smem, (cudaStream_t)stream>>>(d_tables, table_stride, n, (BddlRng*)d_states);

@@ -23,7 +23,7 @@ STAMP = os.path.join(LIB_DIR, "libddl_b200.stamp")
 
 NVCC_FLAGS = [
     "-gencode",
-    "arch=compute_100a,code=sm_100a",
+    "arch=compute_100a,code=[sm_100a,compute_100a]",
     "-lineinfo",
     "-O3",
     "-std=c++17",

@@ -27,6 +27,8 @@ class LoaderConfig:
     # all-SM gather was measured to hold back small kernels of the training stream until it ended.
     fetch_priority: int = 0
     prefetch: bool = True          # launch batch i+1 while batch i is being consumed
+    prefetch_depth: int = 1        # batches assembled ahead of the consumer (needs ring_depth > prefetch_depth)
+    fetch_streams: int = 1         # batch-assembly streams used round-robin (consecutive gathers overlap)
     barrier: str = "auto"          # cross-rank stream barrier: auto | nccl | flags | host
     gather_variant: int = 0        # BDDL_VARIANT_*
     gather_tune: int = 0
@@ -74,5 +76,7 @@ class LoaderConfig:
             raise ValueError(f"unknown exchange {self.exchange!r}")
         if self.residency not in ("hbm", "host") or self.host_stage not in ("gather", "memcpy", "pull"):
             raise ValueError("residency is 'hbm' or 'host'; host_stage is 'gather', 'memcpy' or 'pull'")
+        if self.prefetch_depth < 1 or self.fetch_streams < 1 or self.ring_depth <= self.prefetch_depth:
+            raise ValueError("need prefetch_depth >= 1, fetch_streams >= 1 and ring_depth > prefetch_depth")
         if self.ring_depth < 2:
             raise ValueError("ring_depth must be at least 2")

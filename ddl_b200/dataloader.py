@@ -83,7 +83,7 @@ class DistributedDataLoader(DistributedDataloaderABC):
         self.batch_size = int(batch_size)
         self._finalized = False
         self._lend_seq = 0
-        self._pref: Optional[Tuple[Any, int, Any]] = None
+        self._pref: dict = {}
         self._cur_slot = -1
         self._next_slot = 0
 
@@ -116,7 +116,8 @@ class DistributedDataLoader(DistributedDataloaderABC):
         self._len = self.batches_per_window[0]
         assert self._len > 0
         self._start_access_epoch()
-        self._prefetch(0)
+        for d in range(self.cfg.prefetch_depth):
+            self._prefetch(d)
 
     # -- construction: device transport -------------------------------------------------------------------
     def _init_device(self) -> None:
@@ -139,6 +140,7 @@ class DistributedDataLoader(DistributedDataloaderABC):
         self._views = {}
         self.main = eng.main
         self.fetch = eng.fetch
+        self.fetch_streams = eng.fetch_streams
 
     # -- construction: process transport --------------------------------------------------------------------
     def _init_process(self) -> None:
@@ -158,9 +160,12 @@ class DistributedDataLoader(DistributedDataloaderABC):
         self._consumed = [None] * depth
         if not self.cuda:
             self.main = self.fetch = NullStream()
+            self.fetch_streams = [self.fetch]
             return
         self.main = torch.cuda.current_stream(self.device)
-        self.fetch = torch.cuda.Stream(self.device, priority=-1)
+        self.fetch_streams = [torch.cuda.Stream(self.device, priority=self.cfg.fetch_priority)
+                              for _ in range(self.cfg.fetch_streams)]
+        self.fetch = self.fetch_streams[0]
         lib = N.lib()
         self._win_dev = []
         for (ptr, nbytes) in conn.wins:  # pin + map every borrowed window once
@@ -214,62 +219,63 @@ class DistributedDataLoader(DistributedDataloaderABC):
             data = torch.from_numpy(self.arys[k][start:start + self.batch_size])
             self.metrics.batch(self.batch_size, data.numel() * data.element_size(), 0)
             return torch.split(data, list(self.splits[k]), dim=1)
-        key = (self._lend_seq, b)
-        pref = self._pref
-        if pref is not None and pref[0] == key:
-            slot, ev = pref[1], pref[2]
-        else:
-            slot, ev = self._launch(k, b)
-        self._pref = None
+        hit = self._pref.pop((self._lend_seq, b), None)
+        slot, ev = hit if hit is not None else self._launch(k, b)
         if self.metrics.enabled and self.metrics.timing:
             t0 = time.perf_counter()
             ev.synchronize()
             self.metrics.stall(time.perf_counter() - t0)
         self.main.wait_event(ev)
         self._cur_slot = slot
-        if self.cfg.prefetch and b + 1 < self.batches_per_window[k]:
-            self._prefetch(b + 1)
+        if self.cfg.prefetch:
+            for d in range(1, self.cfg.prefetch_depth + 1):
+                if b + d < self.batches_per_window[k]:
+                    self._prefetch(b + d)
         return self._batch_views(k, slot)
 
     def _prefetch(self, b: int) -> None:
         if not self.cfg.prefetch or (self.transport == "process" and not self.cuda) or self._finalized:
             return
-        k = self.target_rank - 1
-        slot, ev = self._launch(k, b)
-        self._pref = ((self._lend_seq, b), slot, ev)
+        key = (self._lend_seq, b)
+        if key in self._pref or b >= self.batches_per_window[self.target_rank - 1]:
+            return
+        if len(self._pref) > self.cfg.prefetch_depth:  # stale entries of an abandoned window
+            self._pref = {kk: v for kk, v in self._pref.items() if kk[0] == self._lend_seq}
+        self._pref[key] = self._launch(self.target_rank - 1, b)
 
     def _launch(self, k: int, b: int):
         """Enqueue the assembly of batch ``b`` of window ``k`` on the fetch stream."""
         slot = self._next_slot
         self._next_slot = (slot + 1) % len(self._consumed)
+        stream = self.fetch_streams[slot % len(self.fetch_streams)]
         done = self._consumed[slot]
         if done is not None:
-            self.fetch.wait_event(done)  # the training stream has finished with this ring slot
+            stream.wait_event(done)  # the training stream has finished with this ring slot
         B = self.batch_size
         if self.transport == "device":
             eng = self.engine
-            eng.gather(k, self.connection.pushers[k].lent_buf, b * B, slot)
+            eng.gather(k, self.connection.pushers[k].lent_buf, b * B, slot, stream=stream)
             ev = eng.event()
             if eng.cuda:
-                ev.record(eng.fetch)
+                ev.record(stream)
             s = eng.specs[k]
         else:
             s = self.specs[k]
             lib = N.lib()
-            fs = C.c_void_p(self.fetch.cuda_stream)
+            fs = C.c_void_p(stream.cuda_stream)
             plan = self._plans[k]
             if self.cfg.host_pull:
                 p, slots = plan
-                p.run_ptr(slots.data_ptr() + b * B * 8, self._out[slot].data_ptr(), B, self.fetch.cuda_stream)
+                p.run_ptr(slots.data_ptr() + b * B * 8, self._out[slot].data_ptr(), B, stream.cuda_stream)
             else:
                 src = self.connection.wins[k][0] + b * B * s.sample_bytes
                 N.check(lib.bddl_memcpy_async(C.c_void_p(self._stage[slot].data_ptr()), C.c_void_p(src),
                                               B * s.sample_bytes, 1, fs))
                 if plan is not None:
                     p, slots = plan
-                    p.run_ptr(slots[slot].data_ptr(), self._out[slot].data_ptr(), B, self.fetch.cuda_stream)
+                    p.run_ptr(slots[slot].data_ptr(), self._out[slot].data_ptr(), B, stream.cuda_stream)
             ev = torch.cuda.Event()
-            ev.record(self.fetch)
+            ev.record(stream)
         self.metrics.batch(B, B * s.sample_bytes, B * s.out_sample_bytes)
         return slot, ev
 
@@ -314,7 +320,8 @@ class DistributedDataLoader(DistributedDataloaderABC):
             self._end_access_epoch()
             self._advance_to_next_producer()
             self._start_access_epoch()
-            self._prefetch(0)
+            for d in range(self.cfg.prefetch_depth):
+                self._prefetch(d)
 
     def _on_epoch_end(self) -> None:
         self.batch = 0
@@ -336,7 +343,7 @@ class DistributedDataLoader(DistributedDataloaderABC):
         if self._finalized:
             return
         self._finalized = True
-        self._pref = None
+        self._pref = {}
         if self.transport == "device":
             self._views = {}
             self.connection.close()

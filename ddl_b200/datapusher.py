@@ -220,8 +220,8 @@ class DevicePusher:
     # -- one producer iteration ---------------------------------------------------------------------------
     def produce(self) -> None:
         eng, k = self.engine, self.k
-        if self._returned_ev is not None:
-            eng.side.wait_event(self._returned_ev)  # the buffer about to be rewritten is no longer read
+        for ev in self._returned_ev or ():
+            eng.side.wait_event(ev)  # the buffer about to be rewritten is no longer read
         if self.mode == "host":
             if eng.cuda:
                 eng.side.synchronize()  # the previous upload has left the pinned window
@@ -264,7 +264,8 @@ class DevicePusher:
     def lend(self) -> None:
         buf, ev = self._ready
         eng = self.engine
-        eng.fetch.wait_event(ev)
+        for st in eng.fetch_streams:
+            st.wait_event(ev)
         self.lent_buf = buf
         eng.on_lend(self.k, buf)
         if self.run_ahead and not self._stopped:
@@ -272,9 +273,13 @@ class DevicePusher:
 
     def take_back(self) -> None:
         eng = self.engine
-        ev = eng.event()
-        ev.record(eng.fetch) if eng.cuda else None
-        self._returned_ev = ev
+        evs = []
+        for st in eng.fetch_streams:
+            ev = eng.event()
+            if eng.cuda:
+                ev.record(st)
+            evs.append(ev)
+        self._returned_ev = evs
         execute_callbacks("on_shuffle_end", callbacks=self.callbacks, compat=self.compat)
         if not self.run_ahead and not self._stopped:
             self.produce()

@@ -188,9 +188,12 @@ class DeviceEngine:
         if self.cuda:
             self.main = torch.cuda.current_stream(self.device)
             self.side = torch.cuda.Stream(self.device, priority=0)      # table production
-            self.fetch = torch.cuda.Stream(self.device, priority=config.fetch_priority)  # batch assembly
+            self.fetch_streams = [torch.cuda.Stream(self.device, priority=config.fetch_priority)
+                                  for _ in range(config.fetch_streams)]  # batch assembly
+            self.fetch = self.fetch_streams[0]
         else:
             self.main = self.side = self.fetch = NullStream()
+            self.fetch_streams = [self.fetch]
 
         # source table: id g = instance * P + k  ->  that instance's shard k
         n_sources = self.n_instances * self.P
@@ -375,8 +378,9 @@ class DeviceEngine:
         self.cur[k] = nxt
 
     # -- batch assembly (fetch stream) --------------------------------------------------------------
-    def gather(self, k: int, buf: int, first_row: int, ring_slot: int, n: Optional[int] = None) -> None:
+    def gather(self, k: int, buf: int, first_row: int, ring_slot: int, n: Optional[int] = None, stream=None) -> None:
         n = self.B if n is None else n
+        stream = stream or self.fetch
         if self.stage is not None:
             # N9 stage_host: this step's rows, pinned host -> device, then the convert kernel
             s = self.specs[k]
@@ -392,28 +396,28 @@ class DeviceEngine:
                                                    n, s.row_bytes, self.cfg.host_threads))
                 N.check(lib.bddl_memcpy_async(C.c_void_p(self.stage[ring_slot].data_ptr()),
                                               C.c_void_p(self.pinned[ring_slot].data_ptr()), n * s.row_bytes, 1,
-                                              C.c_void_p(self.fetch.cuda_stream)))
+                                              C.c_void_p(stream.cuda_stream)))
                 if ev is None:
                     ev = self.pinned_done[ring_slot] = torch.cuda.Event()
-                ev.record(self.fetch)
+                ev.record(stream)
                 copies.value = 1
             elif self.cfg.host_threads > 1:
                 N.check(lib.bddl_stage_slots_mt(C.c_void_p(self.stage[ring_slot].data_ptr()), s.row_bytes,
                                                 self.h_bases, len(self.h_bases), s.row_bytes, C.c_void_p(slots_ptr),
-                                                n, s.row_bytes, C.c_void_p(self.fetch.cuda_stream),
+                                                n, s.row_bytes, C.c_void_p(stream.cuda_stream),
                                                 self.cfg.host_threads))
                 copies.value = n
             else:
                 N.check(lib.bddl_stage_slots(C.c_void_p(self.stage[ring_slot].data_ptr()), s.row_bytes, self.h_bases,
                                              len(self.h_bases), s.row_bytes, C.c_void_p(slots_ptr), n, s.row_bytes,
-                                             C.c_void_p(self.fetch.cuda_stream), C.byref(copies)))
+                                             C.c_void_p(stream.cuda_stream), C.byref(copies)))
             self.h2d_copies += copies.value
             self.plans[k].run_ptr(self.stage_iota[ring_slot].data_ptr(), self.ring[ring_slot].data_ptr(), n,
-                                  self.fetch.cuda_stream)
+                                  stream.cuda_stream)
             self.launches += 1
         elif self.cuda:
             self.plans[k].run_ptr(self.table_ptr(k, buf, first_row), self.ring[ring_slot].data_ptr(), n,
-                                  self.fetch.cuda_stream)
+                                  stream.cuda_stream)
             self.launches += 1
         else:
             slots = self.tables[k, buf, first_row:first_row + n].numpy()

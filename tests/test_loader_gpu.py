@@ -73,6 +73,8 @@ def test_host_resident_shards(stage):
 def test_prefetch_off_and_deep_ring():
     _run(ddl.LoaderConfig(prefetch=False))
     _run(ddl.LoaderConfig(ring_depth=4))
+    _run(ddl.LoaderConfig(ring_depth=4, prefetch_depth=2, fetch_streams=2))
+    _run(ddl.LoaderConfig(ring_depth=5, prefetch_depth=3, fetch_streams=3, residency="host"), v=16)
 
 
 def test_uint8_images_normalised_to_bf16():
