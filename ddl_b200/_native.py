@@ -123,6 +123,8 @@ def _declare(lib: C.CDLL) -> None:
         "bddl_host_unregister": (C.c_int, [vp]),
         "bddl_stage_rows": (C.c_int, [vp, i64, vp, i64, vp, i64, i64, vp, P(i64)]),
         "bddl_stage_slots": (C.c_int, [vp, i64, vp, i32, i64, vp, i64, i64, vp, P(i64)]),
+        "bddl_batch_checksum_scratch_words": (i64, [i64, i64]),
+        "bddl_batch_checksum": (C.c_int, [vp, i64, i64, i64, vp, i64, vp, vp]),
         "bddl_stage_slots_mt": (C.c_int, [vp, i64, vp, i32, i64, vp, i64, i64, vp, i32]),
         "bddl_host_gather_slots": (C.c_int, [vp, i64, vp, i32, i64, vp, i64, i64, i32]),
         "bddl_stream_wait_value32": (C.c_int, [vp, vp, u32]),

@@ -358,6 +358,26 @@ class DistributedDataLoader(DistributedDataloaderABC):
         self.connection.unlock_windows()
         self.connection.finalize(self.arys)
 
+    def batch_checksum(self) -> torch.Tensor:
+        """Enqueue (on the current stream) the 64-bit fingerprint of the batch handed out last and
+        return the one-element device tensor that will hold it: a cheap per-step result to read
+        back, and the integrity check the reference lacks (csrc/checksum.cu)."""
+        if self._cur_slot < 0 or not self.cuda:
+            raise RuntimeError("batch_checksum needs a batch delivered on a CUDA device")
+        from .ops.checksum import BatchChecksum
+
+        k = self.target_rank - 1
+        if self.transport == "device":
+            s, raw = self.engine.specs[k], self.engine.ring[self._cur_slot]
+        else:
+            s = self.specs[k]
+            raw = self._out[self._cur_slot] if self._plans[k] is not None else \
+                self._stage[self._cur_slot][: self.batch_size * s.sample_bytes].view(self.batch_size, s.sample_bytes)
+        payload = s.out_sample_bytes // 8 * 8
+        if getattr(self, "_checksum", None) is None:
+            self._checksum = BatchChecksum(self.device, self.batch_size, max(8, payload))
+        return self._checksum.run(raw, payload)
+
     def close(self) -> None:
         """Early shutdown (the reference can only stop by running out of epochs)."""
         if not self._finalized:

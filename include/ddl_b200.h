@@ -117,6 +117,14 @@ int bddl_exchange_gather_collate(const bddl_gather_desc* desc, void* stream);
 /* Number of kernels this library has launched in this process (for gpu_launches accounting). */
 int64_t bddl_launch_count(void);
 
+/* ---- Batch checksum (no counterpart: the reference never verifies what a consumer receives,
+ *      tests/test_ddl.py:8-28).  *d_out = sum over the 8-byte words of the batch of
+ *      mix64(word ^ position), rows of payload_bytes at stride row_bytes.  d_scratch: caller-owned
+ *      device memory of at least bddl_batch_checksum_scratch_words() 64-bit words. ------------- */
+int64_t bddl_batch_checksum_scratch_words(int64_t n_rows, int64_t payload_bytes);
+int bddl_batch_checksum(const void* d_batch, int64_t n_rows, int64_t row_bytes, int64_t payload_bytes,
+                        uint64_t* d_scratch, int64_t scratch_words, uint64_t* d_out, void* stream);
+
 /* ---- N7: symmetric heap (replaces MPI.Win.Allocate_shared / Shared_query,
  *      ddl/connection.py:88-139): cudaMalloc segments exported as CUDA IPC handles and mapped
  *      by every peer; pinned, device-mapped host memory for host-resident datasets. ---------- */

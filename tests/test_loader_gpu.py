@@ -103,6 +103,9 @@ def test_uint8_images_normalised_to_bf16():
         for i, (x,) in enumerate(loader):
             ref = (torch.from_numpy(data[order[i * B:(i + 1) * B]]).float() * sc + bi).to(torch.bfloat16)
             assert x.dtype == torch.bfloat16 and torch.equal(x.cpu().view(torch.int16), ref.view(torch.int16))
+            from ddl_b200.ops import checksum_reference
+            got = int(loader.batch_checksum().item()) & (2**64 - 1)
+            assert got == checksum_reference(ref.view(torch.int16).numpy())
             loader.mark(ddl.Marker.END_OF_BATCH)
         loader.mark(ddl.Marker.END_OF_EPOCH)
 
