@@ -122,3 +122,56 @@ extern "C" int bddl_batch_checksum(const void* d_batch, int64_t n_rows, int64_t 
                          (long long)scratch_words, (long long)need);
     return bddl_checksum::launch(d_batch, n_rows, row_bytes, payload_bytes, d_scratch, d_out, (cudaStream_t)stream);
 }
+
+// ---- Entry point for callers that must not allocate ------------------------------------------------
+//
+// Some users of this library cannot call cudaMalloc when they want a fingerprint: a training
+// process that has handed every free byte of HBM to its framework's caching allocator (a fresh
+// cudaMalloc then fails, or forces that allocator to trim); a latency-critical step, because
+// cudaMalloc and cudaFree may synchronise the whole device; a host application that forbids its
+// plug-ins to allocate after start-up.  For them the scratch of the reduction lives in the
+// library image: one file-scope device array of 1 + 8192 words (64 KiB).  Every GPU that loads
+// the library holds that array until the process exits.
+//
+// Consequences of sharing one array:
+//   * size limit: 8192 tiles of 64 KiB, i.e. batches up to 512 MiB; larger ones are refused;
+//   * the array keeps what the previous call left in it -- the ticket word is cleared on the
+//     stream before every launch, the partials are fully rewritten before they are read;
+//   * two calls whose GPU work overlaps on one device (different streams, no ordering between
+//     them) race on the array: order them;
+//   * the first call on each device looks up the array's device address
+//     (cudaGetSymbolAddress); make that first call before any stream capture starts.
+#define BDDL_CHECKSUM_STATIC_MAX_TILES 8192
+
+static __device__ __align__(256) unsigned long long g_checksum_scratch[1 + BDDL_CHECKSUM_STATIC_MAX_TILES];
+
+extern "C" int64_t bddl_batch_checksum_static_max_bytes(void) {
+    return (int64_t)BDDL_CHECKSUM_STATIC_MAX_TILES * bddl_checksum::kTileBytes;
+}
+
+extern "C" int bddl_batch_checksum_static(const void* d_batch, int64_t n_rows, int64_t row_bytes,
+                                          int64_t payload_bytes, uint64_t* d_out, void* stream) {
+    int rc = bddl_checksum::check_args(d_batch, n_rows, row_bytes, payload_bytes, d_out);
+    if (rc) return rc;
+    const int64_t tiles = bddl_checksum::tiles_for(n_rows, payload_bytes);
+    if (tiles > BDDL_CHECKSUM_STATIC_MAX_TILES)
+        return bddl_fail(BDDL_ERR_INVALID,
+                         "batch_checksum_static: batch of %lld bytes exceeds the built-in scratch (limit %lld bytes); "
+                         "use bddl_batch_checksum with caller-owned scratch",
+                         (long long)(n_rows * payload_bytes), (long long)bddl_batch_checksum_static_max_bytes());
+    // In host code `g_checksum_scratch` is only a handle for the symbol, not a device address:
+    // resolve it once per device, with that device current, and hand the result to the kernel.
+    static unsigned long long* resolved[64];
+    int dev = 0;
+    BDDL_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return bddl_fail(BDDL_ERR_INVALID, "batch_checksum_static: device index %d out of range", dev);
+    unsigned long long* scratch = __atomic_load_n(&resolved[dev], __ATOMIC_ACQUIRE);
+    if (!scratch) {
+        void* p = nullptr;
+        BDDL_CUDA(cudaGetSymbolAddress(&p, g_checksum_scratch));
+        scratch = (unsigned long long*)p;
+        __atomic_store_n(&resolved[dev], scratch, __ATOMIC_RELEASE);
+    }
+    return bddl_checksum::launch(d_batch, n_rows, row_bytes, payload_bytes, (uint64_t*)scratch, d_out,
+                                 (cudaStream_t)stream);
+}

@@ -125,6 +125,8 @@ def _declare(lib: C.CDLL) -> None:
         "bddl_stage_slots": (C.c_int, [vp, i64, vp, i32, i64, vp, i64, i64, vp, P(i64)]),
         "bddl_batch_checksum_scratch_words": (i64, [i64, i64]),
         "bddl_batch_checksum": (C.c_int, [vp, i64, i64, i64, vp, i64, vp, vp]),
+        "bddl_batch_checksum_static_max_bytes": (i64, []),
+        "bddl_batch_checksum_static": (C.c_int, [vp, i64, i64, i64, vp, vp]),
         "bddl_stage_slots_mt": (C.c_int, [vp, i64, vp, i32, i64, vp, i64, i64, vp, i32]),
         "bddl_host_gather_slots": (C.c_int, [vp, i64, vp, i32, i64, vp, i64, i64, i32]),
         "bddl_stream_wait_value32": (C.c_int, [vp, vp, u32]),

@@ -125,6 +125,17 @@ int64_t bddl_batch_checksum_scratch_words(int64_t n_rows, int64_t payload_bytes)
 int bddl_batch_checksum(const void* d_batch, int64_t n_rows, int64_t row_bytes, int64_t payload_bytes,
                         uint64_t* d_scratch, int64_t scratch_words, uint64_t* d_out, void* stream);
 
+/* Same fingerprint for callers that cannot allocate device memory (all HBM already owned by a
+ * framework allocator, no tolerance for the device synchronisation cudaMalloc/cudaFree can cause,
+ * or a host that forbids allocation after start-up).  This entry point has no counterpart in the
+ * reference.  Scratch is a 64 KiB array inside the library image, held by every GPU that loads
+ * the library; batches up to bddl_batch_checksum_static_max_bytes() (512 MiB), larger ones are
+ * refused.  Calls that overlap on one GPU race on that array: order them.  The first call on a
+ * device resolves the array's address; make it before any stream capture. */
+int64_t bddl_batch_checksum_static_max_bytes(void);
+int bddl_batch_checksum_static(const void* d_batch, int64_t n_rows, int64_t row_bytes, int64_t payload_bytes,
+                               uint64_t* d_out, void* stream);
+
 /* ---- N7: symmetric heap (replaces MPI.Win.Allocate_shared / Shared_query,
  *      ddl/connection.py:88-139): cudaMalloc segments exported as CUDA IPC handles and mapped
  *      by every peer; pinned, device-mapped host memory for host-resident datasets. ---------- */
