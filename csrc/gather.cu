@@ -45,6 +45,7 @@ struct KParams {
     uint32_t n_items;
     uint32_t chunks_per_sample;
     uint32_t pad_bits;
+    uint32_t filter_lo, filter_hi;  // push form: deliver only sources in [lo, hi); hi == 0 disables
     float scale[BDDL_MAX_CHANNELS];
     float bias[BDDL_MAX_CHANNELS];
 };
@@ -103,6 +104,10 @@ __device__ __forceinline__ Item resolve_item(const KParams& p, uint32_t item) {
     Item it;
     it.in_bytes = len > start ? (uint32_t)min((int64_t)CHUNK, len - start) : 0u;
     it.region_bytes = (uint32_t)min((int64_t)CHUNK, p.sample_bytes - start);
+    if (p.filter_hi != 0 && (source < p.filter_lo || source >= p.filter_hi)) {
+        it.in_bytes = 0;  // another owner pushes this sample
+        it.region_bytes = 0;
+    }
     it.src = base + off + start;
     it.elem0 = (uint32_t)(start / C::IN_ES);
     it.dst = p.dst + (int64_t)s * p.dst_row_bytes + (int64_t)it.elem0 * C::OUT_ES;
@@ -579,6 +584,8 @@ extern "C" int bddl_exchange_gather_collate(const bddl_gather_desc* d, void* str
     p.chan_stride = chan ? (uint32_t)d->chan_stride : 1u;
     p.n_channels = chan ? d->n_channels : 1;
     p.pad_bits = d->pad_bits;
+    p.filter_lo = (uint32_t)d->filter_lo;
+    p.filter_hi = (uint32_t)d->filter_hi;
     for (int i = 0; i < BDDL_MAX_CHANNELS; ++i) {
         p.scale[i] = d->scale[i];
         p.bias[i] = d->bias[i];
@@ -595,7 +602,7 @@ extern "C" int bddl_exchange_gather_collate(const bddl_gather_desc* d, void* str
 
     switch (d->mode) {
         case BDDL_CVT_COPY:
-            if (tma && !var) {
+            if (tma && !var && d->filter_hi == 0) {
                 switch (d->tune) {
                     case 1:
                         return launch_tma_copy<4096, 6>(d, p, st);

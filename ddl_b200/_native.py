@@ -69,6 +69,9 @@ class GatherDesc(C.Structure):
         ("pad_bits", C.c_uint32),
         ("variant", C.c_int32),
         ("max_ctas", C.c_int32),
+        ("filter_lo", C.c_int32),
+        ("filter_hi", C.c_int32),
+        ("reserved", C.c_int32),
         ("tune", C.c_int32),
     ]
 

@@ -254,7 +254,10 @@ class DistributedDataLoader(DistributedDataloaderABC):
         B = self.batch_size
         if self.transport == "device":
             eng = self.engine
-            eng.gather(k, self.connection.pushers[k].lent_buf, b * B, slot, stream=stream)
+            if eng.push:
+                eng.push_step(k, self.connection.pushers[k].lent_buf, b * B, slot, stream)
+            else:
+                eng.gather(k, self.connection.pushers[k].lent_buf, b * B, slot, stream=stream)
             ev = eng.event()
             if eng.cuda:
                 ev.record(stream)
@@ -315,6 +318,8 @@ class DistributedDataLoader(DistributedDataloaderABC):
             if ev is None:
                 ev = self._consumed[self._cur_slot] = torch.cuda.Event()
             ev.record(self.main)  # the "free" flag of this ring slot, in stream-event form
+            if self.engine is not None and self.engine.push:
+                self.engine.release_slot(self._cur_slot, self.main)
         self.batch += 1
         if self.batch % self.batches_per_window[self.target_rank - 1] == 0:
             self._end_access_epoch()

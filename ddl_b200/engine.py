@@ -232,6 +232,9 @@ class DeviceEngine:
                 views = [self.heap.peer_buffer(g // self.P, f"shard{g % self.P}").numpy(
                     np.uint8, (specs[g % self.P].nData, specs[g % self.P].row_bytes)) for g in range(n_sources)]
                 self.plans.append(CpuGather(views, s))
+        self.push = config.exchange == "push" and self.cuda and not self.host_resident
+        if self.push:
+            self.init_push()
         self._barrier_epoch = 0
         self._barrier_tensor = None
         self._flag_pages = None
@@ -422,6 +425,57 @@ class DeviceEngine:
         else:
             slots = self.tables[k, buf, first_row:first_row + n].numpy()
             self.plans[k].run(slots, self.ring[ring_slot])
+
+    # -- push form of the exchange (owner-side stores over NVLink + flags) ---------------------------------
+    # Every rank scans every consumer's batch slice, delivers the samples it owns into that
+    # consumer's ring slot with peer stores, and bumps the consumer's `ready` counter
+    # (red.release.sys).  Consumers wait on their own counter with cuStreamWaitValue32 and hand a
+    # slot back by storing its use count into every owner's `free` word (st.release.sys) -- the
+    # reference's lend/return tokens (ddl/connection.py:153-182) as NVLink-visible counters.
+    _READY0, _FREE0 = 64, 128
+
+    def init_push(self) -> None:
+        R, D = self.n_instances, self.ring_depth
+        if R * 16 + self._FREE0 > 1024 or D > 16:
+            raise ValueError("push exchange supports up to 56 instances and ring_depth <= 16")
+        self._use = [0] * D
+        ready = [[self.heap.peer_ptr(c, "flags") + 4 * (self._READY0 + s) for s in range(D)] for c in range(R)]
+        free = [[self.heap.peer_ptr(o, "flags") + 4 * (self._FREE0 + self.me * 16 + s) for o in range(R)]
+                for s in range(D)]
+        self._ready_targets = torch.tensor(ready, dtype=torch.int64).to(self.device)   # [R, D]
+        self._free_targets = torch.tensor(free, dtype=torch.int64).to(self.device)     # [D, R]
+        self.push_plans = []
+        for s in self.specs:
+            plan = GatherPlan(self.sources, s.row_bytes, s.sample_bytes, s.convert, dst_row_bytes=self.ring_row,
+                              variant=self.cfg.gather_variant, max_ctas=self.cfg.gather_max_ctas,
+                              tune=self.cfg.gather_tune)
+            plan.set_filter(self.me * self.P, (self.me + 1) * self.P)
+            self.push_plans.append(plan)
+
+    def push_step(self, k: int, buf: int, first_row: int, ring_slot: int, stream) -> None:
+        lib, R, n = N.lib(), self.n_instances, self.B
+        sp = C.c_void_p(stream.cuda_stream)
+        use = self._use[ring_slot]
+        flags = self.flags_buf.ptr
+        table_off = ((k * 2 + buf) * self.n_max + first_row) * 8
+        ring_off = ring_slot * self.B * self.ring_row
+        for i in range(R):
+            c = (self.me + i) % R  # staggered so that owners do not all hit one consumer at once
+            if use > 0:  # consumer c must have released the slot's previous contents
+                N.check(lib.bddl_stream_wait_value32(sp, C.c_void_p(flags + 4 * (self._FREE0 + c * 16 + ring_slot)), use))
+            self.push_plans[k].run_ptr(self.heap.peer_ptr(c, "tables") + table_off,
+                                       self.heap.peer_ptr(c, "ring") + ring_off, n, stream.cuda_stream)
+            N.check(lib.bddl_flag_signal(C.c_void_p(self._ready_targets[c, ring_slot:].data_ptr()), 1, 1, 1, sp))
+            self.launches += 2
+        self._use[ring_slot] = use + 1
+        # ... and as a consumer: all R owners have delivered their share of my batch
+        N.check(lib.bddl_stream_wait_value32(sp, C.c_void_p(flags + 4 * (self._READY0 + ring_slot)), R * (use + 1)))
+
+    def release_slot(self, ring_slot: int, stream) -> None:
+        """Consumer side of the push form: tell every owner that `ring_slot` may be refilled."""
+        N.check(N.lib().bddl_flag_signal(C.c_void_p(self._free_targets[ring_slot].data_ptr()), self.n_instances,
+                                         self._use[ring_slot], 0, C.c_void_p(stream.cuda_stream)))
+        self.launches += 1
 
     def on_lend(self, k: int, buf: int) -> None:
         """Called when the consumer borrows window k: host staging needs the table on the host."""

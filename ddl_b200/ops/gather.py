@@ -156,6 +156,10 @@ class GatherPlan:
         self._desc = d
         self._fn = N.lib().bddl_exchange_gather_collate
 
+    def set_filter(self, lo: int, hi: int) -> None:
+        """Push form: deliver only slots whose source id is in [lo, hi) (0, 0 = everything)."""
+        self._desc.filter_lo, self._desc.filter_hi = int(lo), int(hi)
+
     def alloc_batch(self, n_samples: int) -> torch.Tensor:
         """Raw batch buffer [n_samples, dst_row_bytes] uint8 (rows 16-byte aligned)."""
         return torch.empty((n_samples, self.dst_row_bytes), dtype=torch.uint8, device=self.sources.device)

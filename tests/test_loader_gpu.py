@@ -77,6 +77,11 @@ def test_prefetch_off_and_deep_ring():
     _run(ddl.LoaderConfig(ring_depth=5, prefetch_depth=3, fetch_streams=3, residency="host"), v=16)
 
 
+def test_push_exchange_single_gpu():
+    """Owner-side stores + ready/free counters (one rank pushes to itself)."""
+    _run(ddl.LoaderConfig(exchange="push", ring_depth=3, prefetch_depth=2))
+
+
 def test_uint8_images_normalised_to_bf16():
     n, B = 1024, 64
     hw = 24 * 24
@@ -132,6 +137,21 @@ def test_process_transport_consumer_on_gpu(tmp_path):
     _torchrun(3, cfg, tmp_path)
     exp = expected_epochs(1, 2, 4000, 256, 4, 0.5)[0]
     assert np.array_equal(np.load(os.path.join(str(tmp_path), "seen_0.npy")), exp)
+
+
+@pytest.mark.multigpu
+def test_two_gpus_push_exchange(tmp_path):
+    """Push form: every GPU stores the samples it owns into its peer's batch ring over NVLink."""
+    cfg = {"n_instances": 2, "n_producers": 1, "n": 4096, "v": 32, "B": 256, "epochs": 5, "fraction": 0.5,
+           "shuffle_mode": "device", "declare_seed": True, "cpu": False}
+    os.environ["DDL_B200_EXCHANGE"] = "push"
+    try:
+        _torchrun(2, cfg, tmp_path)
+    finally:
+        os.environ.pop("DDL_B200_EXCHANGE", None)
+    exp = expected_epochs(2, 1, 4096, 256, 5, 0.5)
+    for i in range(2):
+        assert np.array_equal(np.load(os.path.join(str(tmp_path), f"seen_{i}.npy")), exp[i])
 
 
 @pytest.mark.multigpu
