@@ -201,7 +201,7 @@ class DistributedDataLoader(DistributedDataloaderABC):
         return self._len
 
     def __iter__(self):
-        i = 0
+        i, self._iter_start = getattr(self, "_iter_start", 0), 0
         while i < self._len:
             yield self[i]
             i += 1
@@ -322,6 +322,7 @@ class DistributedDataLoader(DistributedDataloaderABC):
                 self.engine.release_slot(self._cur_slot, self.main)
         self.batch += 1
         if self.batch % self.batches_per_window[self.target_rank - 1] == 0:
+            self._window_done = True  # every batch of this epoch's window was delivered
             self._end_access_epoch()
             self._advance_to_next_producer()
             self._start_access_epoch()
@@ -330,6 +331,7 @@ class DistributedDataLoader(DistributedDataloaderABC):
 
     def _on_epoch_end(self) -> None:
         self.batch = 0
+        self._window_done = False
         self.epoch += 1
         self.metrics.epoch()
         if not self._can_continue():
@@ -391,8 +393,27 @@ class DistributedDataLoader(DistributedDataloaderABC):
 
     # -- checkpoint (absent in the reference) ---------------------------------------------------
     def state_dict(self) -> dict:
-        d = {"epoch": self.epoch, "batch": self.batch, "target_rank": self.target_rank}
-        if self.transport == "device":
-            d["producers"] = [p.state_dict() for p in self.connection.pushers]
-            d["lent"] = [self.engine.table(p.k, p.lent_buf).cpu().numpy().copy() for p in self.connection.pushers]
-        return d
+        """Everything needed to continue the exact sample sequence: position, slot tables, RNG
+        streams, partner-RNG streams.  Cheap because rows never move: a table is 8 bytes per
+        sample.  Take it between batches (after ``mark(END_OF_BATCH)``), at the same step on
+        every rank."""
+        if self.transport != "device":
+            raise NotImplementedError("checkpoints cover the device transport; host windows are user state")
+        return {"epoch": self.epoch, "batch": self.batch, "target_rank": self.target_rank, "len": self._len,
+                "window_done": getattr(self, "_window_done", False),
+                "producers": [p.state_dict() for p in self.connection.pushers]}
+
+    def load_state_dict(self, d: dict) -> None:
+        """Resume on a freshly constructed loader (same producer function, batch size, world)."""
+        if self.transport != "device":
+            raise NotImplementedError("checkpoints cover the device transport")
+        for p, pd in zip(self.connection.pushers, d["producers"]):
+            p.load_state_dict(pd)
+        self.epoch, self.batch, self.target_rank, self._len = d["epoch"], d["batch"], d["target_rank"], d["len"]
+        self._pref = {}
+        self._lend_seq += 1
+        self._window_done = d.get("window_done", False)
+        # an epoch whose window is finished but not yet marked yields nothing more
+        self._iter_start = self._len if self._window_done else self.batch
+        for i in range(self.cfg.prefetch_depth):
+            self._prefetch(self._iter_start + i)

@@ -296,10 +296,41 @@ class DevicePusher:
             eng.side.synchronize()
         d = {"iterations": self.iterations, "mode": self.mode,
              "table": eng.table(k, self._ready[0]).cpu().numpy().copy(),
+             "lent_table": eng.table(k, self.lent_buf).cpu().numpy().copy(),
+             "lent_is_ready": self.lent_buf == self._ready[0],
              "rng_words": eng.states[k].cpu().numpy().copy()}
         if self.global_shuffler is not None:
             d["shuffler"] = self.global_shuffler.state_dict()
         return d
+
+    def load_state_dict(self, d: dict) -> None:
+        """Restore tables, RNG stream and iteration count (device / trace shuffle modes)."""
+        import torch
+
+        if self.mode == "host":
+            raise NotImplementedError("host-shuffle windows are user state; checkpoint them in the producer function")
+        eng, k = self.engine, self.k
+        if eng.cuda:
+            eng.side.synchronize()
+            for st in eng.fetch_streams:
+                st.synchronize()
+        ready_buf = eng.cur[k]
+        eng.table(k, ready_buf).copy_(torch.from_numpy(d["table"]))
+        if d["lent_is_ready"]:
+            self.lent_buf = ready_buf
+        else:
+            self.lent_buf = 1 - ready_buf
+            eng.table(k, self.lent_buf).copy_(torch.from_numpy(d["lent_table"]))
+        eng.states[k].copy_(torch.from_numpy(d["rng_words"]))
+        self.iterations = d["iterations"]
+        if self.global_shuffler is not None and "shuffler" in d:
+            self.global_shuffler.load_state_dict(d["shuffler"])
+        ev = eng.event()
+        if eng.cuda:
+            torch.cuda.current_stream(eng.device).synchronize()
+            ev.record(eng.side)
+        self._ready = (ready_buf, ev)
+        self._returned_ev = None
 
 
 class _TaggedComm:

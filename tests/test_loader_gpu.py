@@ -77,6 +77,12 @@ def test_prefetch_off_and_deep_ring():
     _run(ddl.LoaderConfig(ring_depth=5, prefetch_depth=3, fetch_streams=3, residency="host"), v=16)
 
 
+def test_checkpoint_resume_on_gpu():
+    import test_checkpoint as tc
+
+    tc.run_resume_case(None)
+
+
 def test_push_exchange_single_gpu():
     """Owner-side stores + ready/free counters (one rank pushes to itself)."""
     _run(ddl.LoaderConfig(exchange="push", ring_depth=3, prefetch_depth=2))
