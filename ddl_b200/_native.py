@@ -130,6 +130,16 @@ def _declare(lib: C.CDLL) -> None:
         "bddl_batch_checksum": (C.c_int, [vp, i64, i64, i64, vp, i64, vp, vp]),
         "bddl_batch_checksum_static_max_bytes": (i64, []),
         "bddl_batch_checksum_static": (C.c_int, [vp, i64, i64, i64, vp, vp]),
+        "bddl_vmm_query": (C.c_int, [i32, P(i32), P(i32), P(i32)]),
+        "bddl_vmm_alloc": (C.c_int, [sz, i32, sz, P(vp), P(u64), P(i32), P(sz)]),
+        "bddl_vmm_import": (C.c_int, [i32, sz, i32, P(vp), P(u64)]),
+        "bddl_vmm_free": (C.c_int, [vp, sz, u64]),
+        "bddl_mc_granularity": (C.c_int, [sz, i32, P(sz)]),
+        "bddl_mc_create": (C.c_int, [sz, i32, P(u64), P(i32)]),
+        "bddl_mc_import": (C.c_int, [i32, P(u64)]),
+        "bddl_mc_add_device": (C.c_int, [u64, i32]),
+        "bddl_mc_bind_and_map": (C.c_int, [u64, u64, sz, i32, P(vp)]),
+        "bddl_multicast_put": (C.c_int, [vp, vp, i64, vp]),
         "bddl_stage_slots_mt": (C.c_int, [vp, i64, vp, i32, i64, vp, i64, i64, vp, i32]),
         "bddl_host_gather_slots": (C.c_int, [vp, i64, vp, i32, i64, vp, i64, i64, i32]),
         "bddl_stream_wait_value32": (C.c_int, [vp, vp, u32]),

@@ -160,6 +160,22 @@ int bddl_host_free(void* host_ptr);
 int bddl_host_register(void* host_ptr, size_t bytes, void** dev_ptr);
 int bddl_host_unregister(void* host_ptr);
 
+/* VMM form of the heap and N6 multicast_put (no counterpart in the reference): physical
+ * allocations shared between processes as POSIX file descriptors, and an NVLS multicast object
+ * every GPU binds memory to; a store through the multicast mapping (multimem.st) is replicated
+ * by NVSwitch into every GPU's copy.  All feature-detected (bddl_vmm_query). */
+int bddl_vmm_query(int32_t dev, int32_t* vmm, int32_t* posix_fd, int32_t* multicast);
+int bddl_vmm_alloc(size_t bytes, int32_t dev, size_t granularity, void** ptr, uint64_t* handle, int32_t* fd,
+                   size_t* rounded);
+int bddl_vmm_import(int32_t fd, size_t size, int32_t dev, void** ptr, uint64_t* handle);
+int bddl_vmm_free(void* ptr, size_t size, uint64_t handle);
+int bddl_mc_granularity(size_t bytes, int32_t n_devices, size_t* gran);
+int bddl_mc_create(size_t size, int32_t n_devices, uint64_t* mc, int32_t* fd);
+int bddl_mc_import(int32_t fd, uint64_t* mc);
+int bddl_mc_add_device(uint64_t mc, int32_t dev);
+int bddl_mc_bind_and_map(uint64_t mc, uint64_t mem_handle, size_t size, int32_t dev, void** mc_ptr);
+int bddl_multicast_put(void* mc_dst, const void* d_src, int64_t bytes, void* stream);
+
 /* ---- N9: stage_host (replaces the window fill, tests/run_ddl.py:152-161, and the absent
  *      .to(device), tests/run_ddl.py:233-235, for host-resident datasets): one cudaMemcpyAsync
  *      per run of adjacent rows from pinned memory into a device staging buffer. ------------- */

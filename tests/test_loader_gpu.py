@@ -175,3 +175,20 @@ def test_two_gpus_global_shuffle_over_nvlink(tmp_path, barrier):
     exp = expected_epochs(2, 2, 4096, 256, 6, 0.5)
     for i in range(2):
         assert np.array_equal(np.load(os.path.join(str(tmp_path), f"seen_{i}.npy")), exp[i])
+
+
+@pytest.mark.multigpu
+def test_replicated_delivery_multicast_or_unicast():
+    """MulticastBuffer: multimem.st through an NVLS multicast object where the platform has it,
+    peer copies otherwise; either way every GPU's copy must hold what the owner wrote."""
+    import socket
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", str(port), os.path.join(HERE, "workers", "run_multicast.py")]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert "MODE" in res.stdout
+    print(res.stdout[res.stdout.index("CAPS"):][:200])
