@@ -22,6 +22,7 @@ __all__ = [
     "init_mpi",
     "init_env",
     "DoesNotMatchError",
+    "LoaderTimeoutError",
 ]
 
 from .config import LoaderConfig
@@ -29,7 +30,8 @@ from .connection import Connection
 from .dataloader import DistributedDataLoader, Marker, ProducerFunctionSkeleton
 from .datapusher import DataProducerOnInitReturn, DataPusher
 from .env import distributed_dataloader, init_mpi
-from .exceptions import DoesNotMatchError
+from . import exceptions
+from .exceptions import DoesNotMatchError, LoaderTimeoutError
 from .ops.gather import Convert
 from .parallel.topology import init_env
 

@@ -254,10 +254,11 @@ class DistributedDataLoader(DistributedDataloaderABC):
         B = self.batch_size
         if self.transport == "device":
             eng = self.engine
-            if eng.push:
-                eng.push_step(k, self.connection.pushers[k].lent_buf, b * B, slot, stream)
-            else:
-                eng.gather(k, self.connection.pushers[k].lent_buf, b * B, slot, stream=stream)
+            with eng.tracer.span("gather", stream):
+                if eng.push:
+                    eng.push_step(k, self.connection.pushers[k].lent_buf, b * B, slot, stream)
+                else:
+                    eng.gather(k, self.connection.pushers[k].lent_buf, b * B, slot, stream=stream)
             ev = eng.event()
             if eng.cuda:
                 ev.record(stream)
@@ -384,6 +385,10 @@ class DistributedDataLoader(DistributedDataloaderABC):
         if getattr(self, "_checksum", None) is None:
             self._checksum = BatchChecksum(self.device, self.batch_size, max(8, payload))
         return self._checksum.run(raw, payload)
+
+    def trace_summary(self) -> dict:
+        """Device-time statistics per loader stage (needs ``LoaderConfig(trace=True)``)."""
+        return self.engine.tracer.summary() if self.engine is not None else {}
 
     def close(self) -> None:
         """Early shutdown (the reference can only stop by running out of epochs)."""

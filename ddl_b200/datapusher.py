@@ -222,6 +222,14 @@ class DevicePusher:
         eng, k = self.engine, self.k
         for ev in self._returned_ev or ():
             eng.side.wait_event(ev)  # the buffer about to be rewritten is no longer read
+        with eng.tracer.span(f"produce.window{k + 1}", eng.side):
+            self._produce_body(eng, k)
+        ev = eng.event()
+        ev.record(eng.side) if eng.cuda else None
+        self._ready = (eng.cur[k], ev)
+        self.iterations += 1
+
+    def _produce_body(self, eng, k) -> None:
         if self.mode == "host":
             if eng.cuda:
                 eng.side.synchronize()  # the previous upload has left the pinned window
@@ -237,10 +245,6 @@ class DevicePusher:
                 eng.local_shuffle(k)
             else:
                 self._trace_shuffle()
-        ev = eng.event()
-        ev.record(eng.side) if eng.cuda else None
-        self._ready = (eng.cur[k], ev)
-        self.iterations += 1
 
     def _trace_shuffle(self) -> None:
         """Run the user's execute_function on a row-id proxy and apply the permutation it made."""

@@ -32,6 +32,7 @@ from .ops import tables as T
 from .ops.gather import SLOT_ROW_BITS, SLOT_ROW_MASK, Convert, GatherPlan, SourceTable, round_up
 from .ops.rng import Pcg64
 from .parallel.heap import SymmetricHeap
+from .utils.tracing import Tracer
 
 log = logging.getLogger("ddl_b200")
 
@@ -153,6 +154,7 @@ class DeviceEngine:
         self.me = env.color
         self.comm = env.comm_nth_pusher if env.transport == "device" else env.comm_global
         self.launches = 0
+        self.tracer = Tracer(config.trace, self.cuda)
 
         # every instance must describe the same windows for the k-th producer (rows are swapped
         # between them); the reference would fail inside MPI with a truncation error instead

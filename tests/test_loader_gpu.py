@@ -83,6 +83,23 @@ def test_checkpoint_resume_on_gpu():
     tc.run_resume_case(None)
 
 
+def test_tracing_reports_device_time_per_stage():
+    got = {}
+
+    @ddl.distributed_dataloader(n_instances=1, n_producers=1, config=ddl.LoaderConfig(trace=True))
+    def main(env, conn):
+        loader = ddl.DistributedDataLoader(IdShard(2048, 8, True), 256, conn, 2, 0.5)
+        for _ in range(2):
+            for a, b in loader:
+                loader.mark(ddl.Marker.END_OF_BATCH)
+            got.update(loader.trace_summary())
+            loader.mark(ddl.Marker.END_OF_EPOCH)
+
+    main()
+    assert got["gather"]["count"] >= 16 and got["gather"]["mean_ms"] > 0
+    assert got["produce.window1"]["count"] >= 2
+
+
 def test_push_exchange_single_gpu():
     """Owner-side stores + ready/free counters (one rank pushes to itself)."""
     _run(ddl.LoaderConfig(exchange="push", ring_depth=3, prefetch_depth=2))

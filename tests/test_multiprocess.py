@@ -81,3 +81,17 @@ def test_device_transport_four_instances_single_producer(tmp_path):
            "shuffle_mode": "device", "declare_seed": True}
     run_world(4, cfg, tmp_path)
     check(tmp_path, 4, 1, cfg)
+
+
+@pytest.mark.timeout(120)
+def test_dead_producer_is_detected_not_hung(tmp_path):
+    """Failure detection: in the reference a dead producer hangs the consumer in
+    Recv forever; here the bounded wait raises LoaderTimeoutError."""
+    cfg = dict({"n_instances": 1, "n": 1000, "v": 4, "B": 100, "epochs": 50, "fraction": 0.0,
+                "die_after": 2, "timeout_s": 3.0}, out=str(tmp_path))
+    env = dict(os.environ, BDDL_TEST_CFG=json.dumps(cfg), OMP_NUM_THREADS="1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), WORKER]
+    subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=100)
+    msg = open(os.path.join(str(tmp_path), "timeout.txt")).read()
+    assert "did not answer" in msg

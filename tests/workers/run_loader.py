@@ -33,6 +33,12 @@ class IdProducer(ddl.ProducerFunctionSkeleton):
         self.my_ary[:, 1:] = (gid[:, None] % 97).astype(np.float32)
 
     def execute_function(self, **kw):
+        self.calls = getattr(self, "calls", 0) + 1
+        if CFG.get("die_after") and self.calls > CFG["die_after"]:
+            import time
+
+            time.sleep(12)  # a producer that stops answering mid-run (fault injection)
+            os._exit(0)
         self.rng.shuffle(self.my_ary)
 
 
@@ -42,6 +48,17 @@ def body(env, conn):
     loader = ddl.DistributedDataLoader(IdProducer(n, v, CFG.get("declare_seed", False), group_size), B, conn, E,
                                        CFG.get("fraction", 0.0), "sendrecv_replace", env.color, env.n_instances)
     seen = []
+    if CFG.get("die_after"):
+        try:
+            for e in range(E):
+                for i, (a, b) in enumerate(loader):
+                    loader.mark(ddl.Marker.END_OF_BATCH)
+                loader.mark(ddl.Marker.END_OF_EPOCH)
+        except ddl.exceptions.LoaderTimeoutError as err:
+            with open(os.path.join(CFG["out"], "timeout.txt"), "w") as fh:
+                fh.write(str(err))
+            os._exit(0)
+        os._exit(3)
     for e in range(E):
         ids = []
         for i, (a, b) in enumerate(loader):
