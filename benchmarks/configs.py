@@ -60,6 +60,7 @@ def main():
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--instances", default="world")
+    ap.add_argument("--storage", type=int, default=0, help="dedicated storage GPUs (producers:consumers = storage:rest)")
     ap.add_argument("--out", default=None)
     args = ap.parse_args()
     rows, nv, dtype, B, cvf, splits = CONFIGS[args.config]
@@ -98,7 +99,7 @@ def main():
         n = env.n_instances
         sample_bytes = nv * np.dtype(dtype).itemsize
         out.update(config=args.config, transport=env.transport, device=str(env.device.type), n_instances=n,
-                   producers_per_instance=env.n_producers, batch_per_instance=B, sample_bytes=sample_bytes,
+                   producers_per_instance=env.n_producers, storage_gpus=env.n_storage, batch_per_instance=B, sample_bytes=sample_bytes,
                    out_dtype=str(x[0].dtype), ms_per_step=round(ms / args.steps, 4),
                    samples_per_s=round(n * B * args.steps / ms * 1e3, 1),
                    input_gbs=round(n * B * args.steps * sample_bytes / ms / 1e6, 1), rank=env.comm_global.rank)
@@ -108,7 +109,8 @@ def main():
 
     n_inst = args.instances if args.instances == "world" else int(args.instances)
     cfg = ddl.LoaderConfig.from_env(metrics=False, ring_depth=4, prefetch_depth=2, fetch_streams=2)
-    ddl.distributed_dataloader(body, n_instances=n_inst, n_producers=None if n_inst != "world" else 1, config=cfg)()
+    ddl.distributed_dataloader(body, n_instances=n_inst, n_producers=None if n_inst != "world" else 1, config=cfg,
+                               n_storage=args.storage)()
     if out.get("rank") == 0:
         out.pop("rank")
         print(json.dumps(out), flush=True)

@@ -122,7 +122,14 @@ class DistributedDataLoader(DistributedDataloaderABC):
     # -- construction: device transport -------------------------------------------------------------------
     def _init_device(self) -> None:
         conn, env = self.connection, self.env
-        pushers = [DevicePusher(conn, env, k + 1) for k in range(env.n_producers)]
+        remote = [None] * env.n_producers
+        if getattr(env, "n_storage", 0) > 0:
+            # the storage rank runs on_init/post_init for this instance's producers and answers
+            # with their metadata (the reference's producer processes do the same)
+            srank = env.storage_rank_of(env.color)
+            env.comm_global.send_obj(self.metadata_to_producer, srank, tag=31)
+            remote = env.comm_global.recv_obj(srank, tag=32)
+        pushers = [DevicePusher(conn, env, k + 1, remote_meta=remote[k]) for k in range(env.n_producers)]
         self.metadata_from_producer: List[MetaData_Producer_To_Consumer] = conn.recv_metadata_as_consumer()
         self.splits = [m.splits for m in self.metadata_from_producer]
         self.batches_per_window = [m.batches_per_window for m in self.metadata_from_producer]
@@ -133,7 +140,7 @@ class DistributedDataLoader(DistributedDataloaderABC):
             p.bind(self.engine)
         eng = self.engine
         eng.side.synchronize()
-        eng.comm.barrier()  # every shard is resident before anyone's kernel may pull from it
+        eng.heap_comm.barrier()  # every shard is resident before anyone's kernel may pull from it
         for p in pushers:
             p.start()
         self._consumed = [None] * eng.ring_depth

@@ -150,8 +150,9 @@ class DevicePusher:
     so even a single producer never stalls the consumer.
     """
 
-    def __init__(self, connection: Connection, env, producer_idx: int):
+    def __init__(self, connection: Connection, env, producer_idx: int, remote_meta=None):
         self.connection, self.env = connection, env
+        self.remote = remote_meta is not None  # the data lives on a dedicated storage GPU
         self.cfg = connection.config
         self.compat = self.cfg.compat == "as_wired"
         self.producer_idx = int(producer_idx)  # 1-based, like the reference's shm rank
@@ -163,9 +164,14 @@ class DevicePusher:
         pf = _private_copy(self.metadata_from_consumer.producer_function)
         self.producer_function = pf
         self.callbacks: List[Any] = [pf]
-        self.on_init_return: DataProducerOnInitReturn = execute_callbacks(
-            "on_init", callbacks=self.callbacks, compat=self.compat, rank_global=self.rank_global)
-        self.metadata_to_consumer = _meta_from_init(self.on_init_return, self.metadata_from_consumer.batch_size)
+        if self.remote:
+            # on_init / post_init ran on the storage rank that holds this producer's shard
+            self.on_init_return = remote_meta
+            self.metadata_to_consumer = remote_meta
+        else:
+            self.on_init_return = execute_callbacks(
+                "on_init", callbacks=self.callbacks, compat=self.compat, rank_global=self.rank_global)
+            self.metadata_to_consumer = _meta_from_init(self.on_init_return, self.metadata_from_consumer.batch_size)
         connection.send_metadata(self.metadata_to_consumer, "producer")
         self.engine = None
         self.my_ary: Optional[np.ndarray] = None
@@ -190,8 +196,10 @@ class DevicePusher:
             raise ValueError("shuffle_mode='device' needs DataProducerOnInitReturn.shuffle_seed")
         self.mode = mode
         self.run_ahead = mode in ("device", "trace")
+        if self.remote and mode != "device":
+            raise ValueError("dedicated storage GPUs need a declared shuffle (shuffle_seed): the window is not local")
 
-        self.my_ary = engine.alloc_window(k)
+        self.my_ary = None if self.remote else engine.alloc_window(k)
         num_exchange = int(self.on_init_return.nData * meta.global_shuffle_fraction_exchange)
         if self.n_instance > 1 and num_exchange > 0:
             if meta.global_shuffle_exchange_method != "sendrecv_replace":
@@ -206,9 +214,10 @@ class DevicePusher:
                 self.global_shuffler = DeviceGlobalShuffler(engine, k, num_exchange, self.n_instance,
                                                             self.env.color, seed=self.producer_idx)
             self.callbacks.append(self.global_shuffler)
-        execute_callbacks("post_init", callbacks=self.callbacks, compat=self.compat, rank_global=self.rank_global,
-                          my_ary=self.my_ary, n_instance=self.n_instance)
-        engine.load_shard(k, self.my_ary)
+        if not self.remote:
+            execute_callbacks("post_init", callbacks=self.callbacks, compat=self.compat,
+                              rank_global=self.rank_global, my_ary=self.my_ary, n_instance=self.n_instance)
+            engine.load_shard(k, self.my_ary)
         engine.init_table(k, Pcg64(seed) if mode == "device" else None)
         if mode == "trace":
             self._proxy = np.arange(self.on_init_return.nData, dtype=np.int64).reshape(-1, 1)

@@ -153,6 +153,10 @@ class DeviceEngine:
         self.n_instances = env.n_instances
         self.me = env.color
         self.comm = env.comm_nth_pusher if env.transport == "device" else env.comm_global
+        # with dedicated storage GPUs the heap spans consumers and storage ranks; shards then live
+        # on `env.storage_rank_of(instance)` instead of on the instance's own GPU
+        self.remote_storage = getattr(env, "n_storage", 0) > 0
+        self.heap_comm = env.comm_global if self.remote_storage else self.comm
         self.launches = 0
         self.tracer = Tracer(config.trace, self.cuda)
 
@@ -165,14 +169,18 @@ class DeviceEngine:
                                         f"producer {k + 1}: window geometry differs between instances")
 
         self.n_max = max(s.nData for s in specs)
-        self.heap = SymmetricHeap(self.comm, self.device)
+        self.heap = SymmetricHeap(self.heap_comm, self.device)
         # host residency: shards stay in pinned, node-shared host memory and every step's rows
         # are copied host->device (N9 stage_host) or pulled by the kernel over PCIe
-        self.host_resident = config.residency == "host" and self.cuda
-        if self.host_resident:
-            self.shards = [self.heap.alloc_host_shared(f"shard{k}", s.nData * s.row_bytes) for k, s in enumerate(specs)]
+        self.host_resident = config.residency == "host" and self.cuda and not self.remote_storage
+        if self.remote_storage:
+            self.shards = []
+        elif self.host_resident:
+            self.shards = [self.heap.alloc_host_shared(f"shard{k}_i{self.me}", s.nData * s.row_bytes)
+                           for k, s in enumerate(specs)]
         else:
-            self.shards = [self.heap.alloc(f"shard{k}", s.nData * s.row_bytes, zero=False) for k, s in enumerate(specs)]
+            self.shards = [self.heap.alloc(f"shard{k}_i{self.me}", s.nData * s.row_bytes, zero=False)
+                           for k, s in enumerate(specs)]
         self.tables_buf = self.heap.alloc("tables", self.P * 2 * self.n_max * 8)
         self.flags_buf = self.heap.alloc("flags", 4096)
         ring_row = max(s.dst_row_bytes for s in specs)
@@ -199,7 +207,8 @@ class DeviceEngine:
 
         # source table: id g = instance * P + k  ->  that instance's shard k
         n_sources = self.n_instances * self.P
-        ptrs = [self.heap.peer_ptr(g // self.P, f"shard{g % self.P}") for g in range(n_sources)]
+        where = env.storage_rank_of if self.remote_storage else (lambda i: i)
+        ptrs = [self.heap.peer_ptr(where(g // self.P), f"shard{g % self.P}_i{g // self.P}") for g in range(n_sources)]
         self.plans: List = []
         self.stage = None
         if self.host_resident and config.host_stage in ("memcpy", "gather"):
@@ -223,7 +232,7 @@ class DeviceEngine:
                 self.pinned_done = [None] * self.ring_depth
         elif self.cuda:
             if self.host_resident:
-                ptrs = [self.heap.peer_dev_ptr(g // self.P, f"shard{g % self.P}") for g in range(n_sources)]
+                ptrs = [self.heap.peer_dev_ptr(g // self.P, f"shard{g % self.P}_i{g // self.P}") for g in range(n_sources)]
             self.sources = SourceTable(ptrs, self.device)
             for s in specs:
                 self.plans.append(GatherPlan(self.sources, s.row_bytes, s.sample_bytes, s.convert,
@@ -231,7 +240,7 @@ class DeviceEngine:
                                              max_ctas=config.gather_max_ctas, tune=config.gather_tune))
         else:
             for k, s in enumerate(specs):
-                views = [self.heap.peer_buffer(g // self.P, f"shard{g % self.P}").numpy(
+                views = [self.heap.peer_buffer(where(g // self.P), f"shard{g % self.P}_i{g // self.P}").numpy(
                     np.uint8, (specs[g % self.P].nData, specs[g % self.P].row_bytes)) for g in range(n_sources)]
                 self.plans.append(CpuGather(views, s))
         self.push = config.exchange == "push" and self.cuda and not self.host_resident
@@ -502,7 +511,7 @@ class DeviceEngine:
         self._closed = True
         if self.cuda:
             torch.cuda.synchronize(self.device)
-        self.comm.barrier()
+        self.heap_comm.barrier()  # storage ranks keep their shards mapped until every consumer is done
         self.tables = None
         self.ring = []
         self.plans = []

@@ -27,7 +27,7 @@ def init_mpi(n_instances: int = 1, **kwargs) -> Env:
 
 
 def distributed_dataloader(func: Optional[Callable] = None, *, n_instances=None, n_producers: Optional[int] = None,
-                           config: Optional[LoaderConfig] = None, world=None, device=None):
+                           config: Optional[LoaderConfig] = None, world=None, device=None, n_storage: int = 0):
     def decorate(f: Callable) -> Callable:
         @functools.wraps(f)
         def wrapper(*args, **kwargs):
@@ -38,11 +38,16 @@ def distributed_dataloader(func: Optional[Callable] = None, *, n_instances=None,
                 import os
 
                 n = world.size if world is not None else int(os.environ.get("WORLD_SIZE", "1"))
-            env = init_env(int(n), world=world, n_producers=n_producers, device=device)
+                n -= n_storage
+            env = init_env(int(n), world=world, n_producers=n_producers, device=device, n_storage=n_storage)
             cfg = config or LoaderConfig.from_env()
             conn = Connection(env.comm_per_gpu_shm, env, cfg)
             result = None
-            if env.is_consumer:
+            if env.is_storage:
+                from .storage import StorageServer
+
+                StorageServer(env, cfg).serve()
+            elif env.is_consumer:
                 result = f(*args, env, conn, **kwargs)
             else:
                 pusher = DataPusher(conn, env.comm_per_gpu_shm, env.comm_nth_pusher, env.comm_global)

@@ -49,10 +49,16 @@ class Env:
     n_producers: int = 1
     device: torch.device = torch.device("cpu")
     consumer_group: Any = None  # torch ProcessGroup of the consumers (the DDP world)
+    n_storage: int = 0          # dedicated storage ranks (GPUs that only hold shards), device transport
+    is_storage: bool = False
 
     @property
     def is_consumer(self) -> bool:
-        return self.comm_per_gpu_shm.rank == 0
+        return self.comm_per_gpu_shm.rank == 0 and not self.is_storage
+
+    def storage_rank_of(self, instance: int) -> int:
+        """World rank whose GPU holds `instance`'s shards (the instance itself without storage ranks)."""
+        return instance if self.n_storage == 0 else self.n_instances + instance % self.n_storage
 
     @property
     def group_size(self) -> int:
@@ -85,10 +91,44 @@ def _pick_device(local_index: int, want_cuda: Optional[bool]) -> torch.device:
     return torch.device("cpu")
 
 
+def _init_env_with_storage(n_instances, n_storage, world, n_producers, device, make_consumer_group) -> Env:
+    """Device transport with dedicated storage GPUs (BASELINE config 4, producers:consumers 1:3):
+    ranks [0, n_instances) consume, ranks [n_instances, n_instances + n_storage) only hold shards.
+    The reference cannot express fewer producers than consumers (ddl/connection.py:29-30)."""
+    comm_global = world.comm
+    rank, size = comm_global.rank, comm_global.size
+    if size != n_instances + n_storage:
+        raise DoesNotMatchError((size, n_instances, n_storage), "world size must be n_instances + n_storage")
+    is_storage = rank >= n_instances
+    role = comm_global.split(1 if is_storage else 0, key=rank, name="role")
+    own = comm_global.split(rank, key=rank, name="per_gpu")
+    comm_global.barrier()
+    if device is None:
+        device = _pick_device(int(os.environ.get("LOCAL_RANK", str(rank))), None)
+    device = torch.device(device)
+    if device.type == "cuda":
+        torch.cuda.set_device(device)
+    group = None
+    try:
+        import torch.distributed as dist
+
+        if make_consumer_group and dist.is_initialized():
+            group = dist.new_group(list(range(n_instances)))
+    except Exception as e:
+        log.warning("could not create the consumer process group: %s", e)
+    producers = int(n_producers if n_producers is not None else os.environ.get("DDL_B200_PRODUCERS", "1"))
+    return Env(comm_global=comm_global, comm_per_gpu=own, comm_per_gpu_shm=own, comm_nth_pusher=role,
+               color=rank if not is_storage else rank - n_instances, color_nth_pusher=0, n_instances=n_instances,
+               world=world, transport="device", n_producers=producers, device=device, consumer_group=group,
+               n_storage=n_storage, is_storage=is_storage)
+
+
 def init_env(n_instances: int = 1, world: Optional[World] = None, n_producers: Optional[int] = None,
-             device: Optional[torch.device] = None, make_consumer_group: bool = True) -> Env:
+             device: Optional[torch.device] = None, make_consumer_group: bool = True, n_storage: int = 0) -> Env:
     """Build the communicators and decide the transport.  Collective over the whole world."""
     world = world or World.from_environment()
+    if n_storage > 0:
+        return _init_env_with_storage(n_instances, n_storage, world, n_producers, device, make_consumer_group)
     comm_global = world.comm
     rank, size = comm_global.rank, comm_global.size
     init_env_error_handling(comm_global, n_instances)

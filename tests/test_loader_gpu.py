@@ -209,3 +209,13 @@ def test_replicated_delivery_multicast_or_unicast():
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "MODE" in res.stdout
     print(res.stdout[res.stdout.index("CAPS"):][:200])
+
+
+@pytest.mark.multigpu
+def test_dedicated_storage_gpu(tmp_path):
+    """One GPU only stores the shards, the other trains: every sample is pulled over NVLink."""
+    cfg = {"n_instances": 1, "n_storage": 1, "n_producers": 2, "n": 4096, "v": 32, "B": 256, "epochs": 4,
+           "fraction": 0.5, "shuffle_mode": "device", "declare_seed": True, "cpu": False}
+    _torchrun(2, cfg, tmp_path)
+    exp = expected_epochs(1, 2, 4096, 256, 4, 0.5)
+    assert np.array_equal(np.load(os.path.join(str(tmp_path), "seen_0.npy")), exp[0])

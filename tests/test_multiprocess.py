@@ -95,3 +95,13 @@ def test_dead_producer_is_detected_not_hung(tmp_path):
     subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=100)
     msg = open(os.path.join(str(tmp_path), "timeout.txt")).read()
     assert "did not answer" in msg
+
+
+@pytest.mark.timeout(200)
+def test_dedicated_storage_ranks_one_to_three(tmp_path):
+    """producers:consumers 1:3 -- one storage rank holds the shards of three consumers, which
+    still see exactly the reference order (inexpressible in the reference, ddl/connection.py:29-30)."""
+    cfg = {"n_instances": 3, "n_storage": 1, "n_producers": 2, "n": 1200, "v": 5, "B": 128, "epochs": 5,
+           "fraction": 0.5, "shuffle_mode": "device", "declare_seed": True}
+    run_world(4, cfg, tmp_path)
+    check(tmp_path, 3, 2, cfg)

@@ -75,5 +75,6 @@ if __name__ == "__main__":
     cfg = ddl.LoaderConfig.from_env(compat=CFG.get("compat"), shuffle_mode=CFG.get("shuffle_mode"),
                                     timeout_s=CFG.get("timeout_s", 120.0))
     main = ddl.distributed_dataloader(body, n_instances=CFG["n_instances"], n_producers=CFG.get("n_producers"),
-                                      config=cfg, device="cpu" if CFG.get("cpu", True) else None)
+                                      config=cfg, device="cpu" if CFG.get("cpu", True) else None,
+                                      n_storage=CFG.get("n_storage", 0))
     main()
