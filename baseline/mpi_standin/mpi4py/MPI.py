@@ -245,18 +245,38 @@ class Intracomm:
         return Request("recv", key, key + "/ack")
 
     def Sendrecv_replace(self, buf, dest, sendtag=0, source=0, recvtag=0):
+        """Bulk payloads travel through a POSIX shared-memory segment (all ranks share the node);
+        only the segment's name goes through the store."""
         arr = np.asarray(buf)
         flat = arr.reshape(-1).view(np.uint8)
-        chunk = 64 << 20
-        n = max(1, (flat.size + chunk - 1) // chunk)
         seq = self._next("bs", dest, sendtag)
-        for i in range(n):
-            _set(f"{self.cid}/b/{self.rank}>{dest}/{sendtag}/{seq}/{i}", flat[i * chunk:(i + 1) * chunk].tobytes())
+        key_s = f"{self.cid}/b/{self.rank}>{dest}/{sendtag}/{seq}"
+        seg = None
+        if flat.size:
+            name = f"bddlmpi_{os.environ.get('BDDL_MPI_SESSION', 'x')}_sr_{abs(hash(key_s)) % (1 << 60):x}"
+            seg = shared_memory.SharedMemory(name=name, create=True, size=flat.size)
+            np.frombuffer(seg.buf, dtype=np.uint8, count=flat.size)[:] = flat
+            _set(key_s, name.encode())
+        else:
+            _set(key_s, b"")
         seq = self._next("br", source, recvtag)
-        for i in range(n):
-            key = f"{self.cid}/b/{source}>{self.rank}/{recvtag}/{seq}/{i}"
-            flat[i * chunk:(i + 1) * chunk] = np.frombuffer(_get(key), dtype=np.uint8)
-            _del(key)
+        key_r = f"{self.cid}/b/{source}>{self.rank}/{recvtag}/{seq}"
+        name = _get(key_r).decode()
+        if name:
+            src = shared_memory.SharedMemory(name=name)
+            try:
+                resource_tracker.unregister(src._name, "shared_memory")
+            except Exception:
+                pass
+            flat[:] = np.frombuffer(src.buf, dtype=np.uint8, count=flat.size)
+            src.close()
+        _del(key_r)
+        _set(key_r + "/ack", b"1")
+        _get(key_s + "/ack")  # the receiver has copied my payload
+        _del(key_s + "/ack")
+        if seg is not None:
+            seg.close()
+            seg.unlink()
 
     # -- collectives --------------------------------------------------------------------------------------
     def Ibarrier(self):

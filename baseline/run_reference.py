@@ -28,7 +28,7 @@ import mpirun  # noqa: E402
 SAMPLE = 3 * 224 * 224
 
 
-def _one_run(n_inst, producers, rows, batch, steps, warmup, e2e, wiring_fix, fraction, timeout=1500):
+def _one_run(n_inst, producers, rows, batch, steps, warmup, e2e, wiring_fix, fraction, timeout=420):
     out = tempfile.mkdtemp(prefix="bddl_ref_")
     bpw = rows // batch
     total = steps + warmup + 1
@@ -65,8 +65,8 @@ def run_reference(args) -> dict:
     if err:
         return {"impl": "reference", "unavailable": err}
     value = n * args.batch * steps / (ms * 1e-3)
-    ms_e, err_e = _one_run(n, producers, rows, args.batch, steps, warmup, True, False, args.fraction)
-    ms_w, err_w = _one_run(n, producers, rows, args.batch, steps, warmup, False, True, args.fraction)
+    ms_e, err_e = _one_run(n, producers, rows, args.batch, steps, warmup, True, False, args.fraction, timeout=300)
+    ms_w, err_w = _one_run(n, producers, rows, args.batch, steps, warmup, False, True, args.fraction, timeout=300)
     return {
         "metric": "gpu_delivered_samples_per_s", "value": round(value, 1), "unit": "samples/s", "n_gpus": n,
         "steps": steps, "warmup": warmup, "ms_per_step": round(ms / steps, 4), "higher_is_better": True,
