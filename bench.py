@@ -188,7 +188,7 @@ def run_ours(args) -> dict:
 
     cfg = ddl.LoaderConfig.from_env(metrics=False, ring_depth=args.ring, gather_variant=args.variant,
                                     gather_tune=args.tune, prefetch_depth=args.prefetch_depth,
-                                    fetch_streams=args.fetch_streams)
+                                    fetch_streams=args.fetch_streams, exchange=args.exchange)
     if not args.e2e_only:
         ddl.distributed_dataloader(body, n_instances="world", n_producers=1, config=cfg)()
     else:
@@ -226,7 +226,7 @@ def run_ours(args) -> dict:
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"model": "imagenet_u8_3x224x224_loader", "global_batch": args.batch * args.gpus,
                    "seq_len": SAMPLE, "parallelism": f"dp{args.gpus}", "per_gpu_batch": args.batch,
-                   "rows_per_gpu": args.rows, "fraction_exchange": args.fraction,
+                   "rows_per_gpu": args.rows, "fraction_exchange": args.fraction, "exchange": args.exchange,
                    "l2": "inputs larger than L2 (shard %.1f GB per GPU, every row read once per epoch)"
                          % (args.rows * SAMPLE / 1e9)},
         "clocks": result["clocks"], "e2e": e2e, "gpu_launches": int(result["launches"]),
@@ -249,6 +249,7 @@ def main():
     ap.add_argument("--tune", type=int, default=0)
     ap.add_argument("--prefetch-depth", type=int, default=3)
     ap.add_argument("--fetch-streams", type=int, default=3)
+    ap.add_argument("--exchange", default="pull", choices=["pull", "push"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-only", action="store_true")
     ap.add_argument("--e2e-variant", type=int, default=0)

@@ -34,6 +34,10 @@ class LoaderConfig:
     gather_tune: int = 0
     gather_max_ctas: int = 0       # SM budget of the batch-assembly kernel (0 = all SMs)
     exchange: str = "pull"         # pull | push
+    # push form: how a stream waits for a counter.  "kernel" = one-thread bounded acquire-poll
+    # kernel; "stream" = cuStreamWaitValue32 (no SM, but a blocked wait sits at the head of its
+    # hardware queue and can hold back unrelated streams that share the queue)
+    push_wait: str = "stream"
     host_pull: bool = False        # process transport: kernel reads the pinned window directly
     residency: str = "hbm"         # device transport: shards in "hbm" or in pinned "host" memory
     # host residency: "gather" (threaded CPU gather into a pinned buffer + one cudaMemcpyAsync),

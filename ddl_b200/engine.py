@@ -450,6 +450,7 @@ class DeviceEngine:
         if R * 16 + self._FREE0 > 1024 or D > 16:
             raise ValueError("push exchange supports up to 56 instances and ring_depth <= 16")
         self._use = [0] * D
+        self._wait_status = torch.zeros(1, dtype=torch.int32, device=self.device)
         ready = [[self.heap.peer_ptr(c, "flags") + 4 * (self._READY0 + s) for s in range(D)] for c in range(R)]
         free = [[self.heap.peer_ptr(o, "flags") + 4 * (self._FREE0 + self.me * 16 + s) for o in range(R)]
                 for s in range(D)]
@@ -463,6 +464,15 @@ class DeviceEngine:
             plan.set_filter(self.me * self.P, (self.me + 1) * self.P)
             self.push_plans.append(plan)
 
+    def _wait_flag(self, sp, addr: int, value: int) -> None:
+        lib = N.lib()
+        if self.cfg.push_wait == "stream":
+            N.check(lib.bddl_stream_wait_value32(sp, C.c_void_p(addr), value))
+        else:
+            N.check(lib.bddl_flag_wait(C.c_void_p(addr), value, int(self.cfg.timeout_s * 2e6), None,
+                                       C.c_void_p(self._wait_status.data_ptr()), sp))
+            self.launches += 1
+
     def push_step(self, k: int, buf: int, first_row: int, ring_slot: int, stream) -> None:
         lib, R, n = N.lib(), self.n_instances, self.B
         sp = C.c_void_p(stream.cuda_stream)
@@ -473,14 +483,14 @@ class DeviceEngine:
         for i in range(R):
             c = (self.me + i) % R  # staggered so that owners do not all hit one consumer at once
             if use > 0:  # consumer c must have released the slot's previous contents
-                N.check(lib.bddl_stream_wait_value32(sp, C.c_void_p(flags + 4 * (self._FREE0 + c * 16 + ring_slot)), use))
+                self._wait_flag(sp, flags + 4 * (self._FREE0 + c * 16 + ring_slot), use)
             self.push_plans[k].run_ptr(self.heap.peer_ptr(c, "tables") + table_off,
                                        self.heap.peer_ptr(c, "ring") + ring_off, n, stream.cuda_stream)
             N.check(lib.bddl_flag_signal(C.c_void_p(self._ready_targets[c, ring_slot:].data_ptr()), 1, 1, 1, sp))
             self.launches += 2
         self._use[ring_slot] = use + 1
         # ... and as a consumer: all R owners have delivered their share of my batch
-        N.check(lib.bddl_stream_wait_value32(sp, C.c_void_p(flags + 4 * (self._READY0 + ring_slot)), R * (use + 1)))
+        self._wait_flag(sp, flags + 4 * (self._READY0 + ring_slot), R * (use + 1))
 
     def release_slot(self, ring_slot: int, stream) -> None:
         """Consumer side of the push form: tell every owner that `ring_slot` may be refilled."""

@@ -39,8 +39,21 @@ def distributed_dataloader(func: Optional[Callable] = None, *, n_instances=None,
 
                 n = world.size if world is not None else int(os.environ.get("WORLD_SIZE", "1"))
                 n -= n_storage
-            env = init_env(int(n), world=world, n_producers=n_producers, device=device, n_storage=n_storage)
             cfg = config or LoaderConfig.from_env()
+            if cfg.exchange == "push":
+                # the push form parks streams in cuStreamWaitValue32; with the default 8 hardware
+                # queues an unrelated stream (NCCL, the table stream) can end up queued behind a
+                # parked one and the ranks deadlock.  Must be set before the CUDA context exists.
+                import os
+
+                import torch
+
+                if "CUDA_DEVICE_MAX_CONNECTIONS" not in os.environ:
+                    if torch.cuda.is_initialized():
+                        log.warning("exchange='push': CUDA is already initialised; start the process with "
+                                    "CUDA_DEVICE_MAX_CONNECTIONS=32 to rule out false stream dependencies")
+                    os.environ["CUDA_DEVICE_MAX_CONNECTIONS"] = "32"
+            env = init_env(int(n), world=world, n_producers=n_producers, device=device, n_storage=n_storage)
             conn = Connection(env.comm_per_gpu_shm, env, cfg)
             result = None
             if env.is_storage:
