@@ -43,6 +43,7 @@ struct KParams {
     uint32_t chan_stride;
     int32_t n_channels;
     uint32_t n_items;
+    uint32_t n_samples;
     uint32_t chunks_per_sample;
     uint32_t pad_bits;
     uint32_t filter_lo, filter_hi;  // push form: deliver only sources in [lo, hi); hi == 0 disables
@@ -84,8 +85,11 @@ struct Item {
 template <int MODE, int CHUNK>
 __device__ __forceinline__ Item resolve_item(const KParams& p, uint32_t item) {
     using C = Cvt<MODE>;
-    const uint32_t s = item / p.chunks_per_sample;
-    const uint32_t c = item - s * p.chunks_per_sample;
+    // chunk-major order: neighbouring warps work on the same chunk index of *different* samples,
+    // so a batch of few, huge samples still spreads its loads over all owners' NVLink ports
+    // instead of draining one owner at a time
+    const uint32_t c = item / p.n_samples;
+    const uint32_t s = item - c * p.n_samples;
     const uint64_t slot = __ldg(p.slots + s);
     const uint32_t source = (uint32_t)(slot >> BDDL_SLOT_ROW_BITS);
     const uint64_t row = slot & kRowMask;
@@ -584,6 +588,7 @@ extern "C" int bddl_exchange_gather_collate(const bddl_gather_desc* d, void* str
     p.chan_stride = chan ? (uint32_t)d->chan_stride : 1u;
     p.n_channels = chan ? d->n_channels : 1;
     p.pad_bits = d->pad_bits;
+    p.n_samples = (uint32_t)d->n_samples;
     p.filter_lo = (uint32_t)d->filter_lo;
     p.filter_hi = (uint32_t)d->filter_hi;
     for (int i = 0; i < BDDL_MAX_CHANNELS; ++i) {
