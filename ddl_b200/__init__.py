@@ -30,7 +30,7 @@ from .connection import Connection
 from .dataloader import DistributedDataLoader, Marker, ProducerFunctionSkeleton
 from .datapusher import DataProducerOnInitReturn, DataPusher
 from .env import distributed_dataloader, init_mpi
-from . import exceptions
+from . import exceptions, ops
 from .exceptions import DoesNotMatchError, LoaderTimeoutError
 from .ops.gather import Convert
 from .parallel.topology import init_env

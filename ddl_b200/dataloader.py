@@ -233,7 +233,7 @@ class DistributedDataLoader(DistributedDataloaderABC):
             ev.synchronize()
             self.metrics.stall(time.perf_counter() - t0)
         self.main.wait_event(ev)
-        self._cur_slot = slot
+        self._cur_slot, self._cur_batch = slot, b
         if self.cfg.prefetch:
             for d in range(1, self.cfg.prefetch_depth + 1):
                 if b + d < self.batches_per_window[k]:
@@ -372,6 +372,14 @@ class DistributedDataLoader(DistributedDataloaderABC):
         self.connection.Barrier()
         self.connection.unlock_windows()
         self.connection.finalize(self.arys)
+
+    def batch_lengths(self) -> torch.Tensor:
+        """Valid elements per sample of the batch handed out last (variable_length windows)."""
+        if self.transport != "device" or not self.engine.specs[self.target_rank - 1].var:
+            raise RuntimeError("batch_lengths is defined for variable_length windows of the device transport")
+        k = self.target_rank - 1
+        b = self._cur_batch
+        return self.engine.batch_lengths(k, self.connection.pushers[k].lent_buf, b * self.batch_size, self.batch_size)
 
     def batch_checksum(self) -> torch.Tensor:
         """Enqueue (on the current stream) the 64-bit fingerprint of the batch handed out last and

@@ -36,7 +36,7 @@ def _meta_from_init(ret: DataProducerOnInitReturn, batch_size: int) -> MetaData_
     return MetaData_Producer_To_Consumer(
         nData=ret.nData, nValues=ret.nValues, shape=tuple(ret.shape), splits=tuple(ret.splits),
         batches_per_window=bpw, dtype=getattr(ret, "dtype", np.float32), convert=getattr(ret, "convert", None),
-        shuffle_seed=getattr(ret, "shuffle_seed", None))
+        shuffle_seed=getattr(ret, "shuffle_seed", None), variable_length=getattr(ret, "variable_length", False))
 
 
 def _private_copy(obj):
@@ -218,6 +218,12 @@ class DevicePusher:
             execute_callbacks("post_init", callbacks=self.callbacks, compat=self.compat,
                               rank_global=self.rank_global, my_ary=self.my_ary, n_instance=self.n_instance)
             engine.load_shard(k, self.my_ary)
+        if engine.specs[k].var:
+            lens = getattr(self.producer_function, "lengths", None)
+            if self.remote or lens is None:
+                raise ValueError("variable_length windows need producer_function.lengths after post_init "
+                                 "(and are not supported on dedicated storage GPUs yet)")
+            engine.set_lengths(k, np.asarray(lens))
         engine.init_table(k, Pcg64(seed) if mode == "device" else None)
         if mode == "trace":
             self._proxy = np.arange(self.on_init_return.nData, dtype=np.int64).reshape(-1, 1)

@@ -85,6 +85,7 @@ class WindowSpec:
         self.row_bytes = round_up(self.sample_bytes, 16)
         self.convert: Convert = meta.convert if meta.convert is not None else Convert.copy()
         self.splits = tuple(int(s) for s in meta.splits)
+        self.var = bool(getattr(meta, "variable_length", False))
         if self.convert.mode == N.CVT_COPY:
             self.out_dtype = _TORCH_OF_NP[self.np_dtype]
             self.out_elem = self.np_dtype.itemsize
@@ -108,6 +109,8 @@ class CpuGather:
     def __init__(self, shards: Sequence[np.ndarray], spec: WindowSpec):
         self.shards, self.spec = shards, spec
 
+    lengths = None  # [n_sources, n_max] valid elements per row (variable-size windows)
+
     def run(self, slots: np.ndarray, out_raw: torch.Tensor) -> None:
         sp = self.spec
         slots = slots.astype(np.int64)
@@ -118,6 +121,9 @@ class CpuGather:
             m = src == s
             raw[m] = self.shards[int(s)][row[m], :sp.sample_bytes]
         cv = sp.convert
+        if self.lengths is not None:
+            self._run_padded(raw, self.lengths[src, row], out_raw)
+            return
         dst = out_raw[:slots.size, :sp.out_sample_bytes]
         if cv.mode == N.CVT_COPY:
             dst.copy_(torch.from_numpy(raw))
@@ -139,6 +145,28 @@ class CpuGather:
                 bi = torch.tensor(cv.bias[0], dtype=torch.float32)
             y = (t.to(torch.float32) * sc + bi).to(cv.out_dtype)
         dst.copy_(y.contiguous().view(torch.uint8).view(slots.size, -1))
+
+
+def _cpu_run_padded(self, raw: np.ndarray, lens: np.ndarray, out_raw: torch.Tensor) -> None:
+    """Variable-size rows on the CPU path: convert the valid prefix, pad the rest."""
+    sp, cv = self.spec, self.spec.convert
+    n = raw.shape[0]
+    typed = torch.from_numpy(raw.view(sp.np_dtype))
+    if cv.mode == N.CVT_COPY:
+        y = typed.clone()
+        pad = torch.tensor(cv.pad_value).to(y.dtype)
+    elif cv.mode == N.CVT_I32_I64:
+        y = typed.to(torch.int64)
+        pad = torch.tensor(int(cv.pad_value), dtype=torch.int64)
+    else:
+        y = (typed.to(torch.float32) * cv.scale[0] + cv.bias[0]).to(cv.out_dtype)
+        pad = torch.tensor(cv.pad_value, dtype=cv.out_dtype)
+    mask = torch.arange(y.shape[1])[None, :] >= torch.from_numpy(lens.astype(np.int64))[:, None]
+    y[mask] = pad
+    out_raw[:n, :sp.out_sample_bytes].copy_(y.contiguous().view(torch.uint8).view(n, -1))
+
+
+CpuGather._run_padded = _cpu_run_padded
 
 
 class DeviceEngine:
@@ -301,6 +329,41 @@ class DeviceEngine:
         src = data.reshape(s.nData, -1).view(torch.uint8)
         with torch.cuda.stream(self.side) if self.cuda else NullStream():
             dst[:, :s.sample_bytes].copy_(src)
+
+    # -- variable-size windows ------------------------------------------------------------------------
+    def set_lengths(self, k: int, lens_elems: np.ndarray) -> None:
+        """Collective over the consumers: every rank learns every instance's row lengths of window
+        k (4 bytes per sample), so the kernel finds a sample's length locally and only its valid
+        bytes cross NVLink; the rest of the batch row is padded while collating."""
+        s = self.specs[k]
+        if lens_elems.shape != (s.nData,) or lens_elems.min() < 0 or lens_elems.max() > s.nValues:
+            raise ValueError(f"lengths must be {s.nData} values in [0, {s.nValues}]")
+        everyone = self.comm.allgather_obj(lens_elems.astype(np.int32))
+        n_sources = self.n_instances * self.P
+        if not hasattr(self, "lens_all"):
+            self.lens_all = torch.zeros((n_sources, self.n_max), dtype=torch.int32)
+        for i, l in enumerate(everyone):
+            self.lens_all[i * self.P + k, :s.nData] = torch.from_numpy(l)
+        if not self.cuda:
+            self.plans[k].lengths = self.lens_all.numpy()
+            return
+        if self.stage is not None or self.push:
+            raise NotImplementedError("variable-size windows use the HBM/zero-copy pull path")
+        es = s.np_dtype.itemsize
+        self.lens_all_dev = self.lens_all.to(self.device)                           # elements
+        self._lens_dev = (self.lens_all * es).to(self.device)                       # payload bytes
+        self._offs_dev = (torch.arange(self.n_max, dtype=torch.int64) * s.row_bytes).to(self.device)
+        table = self.sources.with_lengths([self._offs_dev] * n_sources, [self._lens_dev[g] for g in range(n_sources)])
+        self.plans[k] = GatherPlan(table, 0, s.sample_bytes, s.convert, dst_row_bytes=self.ring_row,
+                                   variant=self.cfg.gather_variant, max_ctas=self.cfg.gather_max_ctas,
+                                   tune=self.cfg.gather_tune)
+
+    def batch_lengths(self, k: int, buf: int, first_row: int, n: int) -> torch.Tensor:
+        """Valid elements of each sample of a batch (int32 [n]) for variable-size windows."""
+        slots = self.tables[k, buf, first_row:first_row + n]
+        src, row = (slots >> SLOT_ROW_BITS) & 0xFFFF, slots & SLOT_ROW_MASK
+        lens = self.lens_all_dev if self.cuda else self.lens_all
+        return lens[src, row]
 
     # -- table production (side stream) -----------------------------------------------------------
     def init_table(self, k: int, rng: Optional[Pcg64]) -> None:

@@ -124,6 +124,15 @@ class SourceTable:
             self.offsets = torch.tensor([o.data_ptr() for o in offsets], dtype=torch.int64).to(self.device)
             self.lengths = torch.tensor([l.data_ptr() for l in lengths], dtype=torch.int64).to(self.device)
 
+    def with_lengths(self, offsets: Sequence[torch.Tensor], lengths: Sequence[torch.Tensor]) -> "SourceTable":
+        """The same sources, described as variable-size (CSR offsets + payload lengths)."""
+        t = SourceTable.__new__(SourceTable)
+        t.device, t.n_sources, t.base = self.device, self.n_sources, self.base
+        t._keep = (offsets, lengths)
+        t.offsets = torch.tensor([o.data_ptr() for o in offsets], dtype=torch.int64).to(self.device)
+        t.lengths = torch.tensor([l.data_ptr() for l in lengths], dtype=torch.int64).to(self.device)
+        return t
+
 
 class GatherPlan:
     """A reusable launch description: everything but the slot list and the destination."""

@@ -34,7 +34,10 @@ class DataProducerOnInitReturn:
     dtype: element type of the window.  convert: a ``ddl_b200.ops.Convert`` applied while the
     batch is assembled (for example uint8 -> normalised bf16).  shuffle_seed: declare the
     per-iteration local shuffle as ``default_rng(shuffle_seed).shuffle(window)`` so that it runs
-    on the GPU (perm_gen) instead of calling ``execute_function``.
+    on the GPU (perm_gen) instead of calling ``execute_function``.  variable_length: rows are
+    padded to nValues in the window, and after ``post_init`` the producer function exposes
+    ``self.lengths`` (valid elements per row); only the valid part of a sample crosses NVLink and
+    the batch is padded with ``convert.pad_value`` while it is collated.
     """
 
     nData: int
@@ -44,6 +47,7 @@ class DataProducerOnInitReturn:
     dtype: Any = np.float32
     convert: Any = None
     shuffle_seed: Optional[int] = None
+    variable_length: bool = False
 
 
 @dataclasses.dataclass
@@ -68,3 +72,4 @@ class MetaData_Producer_To_Consumer:
     dtype: Any = np.float32
     convert: Any = None
     shuffle_seed: Optional[int] = None
+    variable_length: bool = False
