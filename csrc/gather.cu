@@ -46,6 +46,7 @@ struct KParams {
     uint32_t n_samples;
     uint32_t chunks_per_sample;
     uint32_t pad_bits;
+    uint32_t col_off;               // byte offset of the delivered column slice inside a row
     uint32_t filter_lo, filter_hi;  // push form: deliver only sources in [lo, hi); hi == 0 disables
     float scale[BDDL_MAX_CHANNELS];
     float bias[BDDL_MAX_CHANNELS];
@@ -112,7 +113,7 @@ __device__ __forceinline__ Item resolve_item(const KParams& p, uint32_t item) {
         it.in_bytes = 0;  // another owner pushes this sample
         it.region_bytes = 0;
     }
-    it.src = base + off + start;
+    it.src = base + off + p.col_off + start;
     it.elem0 = (uint32_t)(start / C::IN_ES);
     it.dst = p.dst + (int64_t)s * p.dst_row_bytes + (int64_t)it.elem0 * C::OUT_ES;
     return it;
@@ -563,7 +564,9 @@ extern "C" int bddl_exchange_gather_collate(const bddl_gather_desc* d, void* str
                          (long long)d->dst_row_bytes);
     const bool var = d->d_src_offsets != nullptr;
     if (var && !d->d_src_lengths) return bddl_fail(BDDL_ERR_INVALID, "gather: offsets without lengths");
-    if (!var && ((d->row_bytes & 15) || d->row_bytes < d->sample_bytes))
+    if (d->col_offset_bytes < 0 || (d->col_offset_bytes & 15) || (var && d->col_offset_bytes))
+        return bddl_fail(BDDL_ERR_INVALID, "gather: col_offset_bytes must be a non-negative multiple of 16 (fixed-size rows)");
+    if (!var && ((d->row_bytes & 15) || d->row_bytes < d->sample_bytes + d->col_offset_bytes))
         return bddl_fail(BDDL_ERR_INVALID, "gather: shard row stride %lld must be a multiple of 16 and >= %lld",
                          (long long)d->row_bytes, (long long)d->sample_bytes);
     static const int in_es[] = {1, 1, 4, 1, 4}, out_es[] = {1, 2, 2, 4, 8};
@@ -589,6 +592,7 @@ extern "C" int bddl_exchange_gather_collate(const bddl_gather_desc* d, void* str
     p.n_channels = chan ? d->n_channels : 1;
     p.pad_bits = d->pad_bits;
     p.n_samples = (uint32_t)d->n_samples;
+    p.col_off = (uint32_t)d->col_offset_bytes;
     p.filter_lo = (uint32_t)d->filter_lo;
     p.filter_hi = (uint32_t)d->filter_hi;
     for (int i = 0; i < BDDL_MAX_CHANNELS; ++i) {

@@ -71,7 +71,7 @@ class GatherDesc(C.Structure):
         ("max_ctas", C.c_int32),
         ("filter_lo", C.c_int32),
         ("filter_hi", C.c_int32),
-        ("reserved", C.c_int32),
+        ("col_offset_bytes", C.c_int32),
         ("tune", C.c_int32),
     ]
 

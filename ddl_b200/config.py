@@ -44,6 +44,10 @@ class LoaderConfig:
     # "memcpy" (one cudaMemcpyAsync per row run) or "pull" (kernel reads host memory, zero-copy)
     host_stage: str = "pull"
     host_threads: int = 4
+    # sequence/context parallelism: deliver only columns [seq_rank, seq_rank+1) * nValues/seq_size of
+    # every sample (single-field windows); the rest of the row never leaves its owner
+    seq_rank: int = 0
+    seq_size: int = 1
     timeout_s: float = 600.0       # bounded waits: a dead producer raises instead of hanging
     metrics: bool = True
     trace: bool = False            # CUDA-event timing of every loader stage

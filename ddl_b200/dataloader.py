@@ -133,7 +133,8 @@ class DistributedDataLoader(DistributedDataloaderABC):
         self.metadata_from_producer: List[MetaData_Producer_To_Consumer] = conn.recv_metadata_as_consumer()
         self.splits = [m.splits for m in self.metadata_from_producer]
         self.batches_per_window = [m.batches_per_window for m in self.metadata_from_producer]
-        specs = [WindowSpec(m) for m in self.metadata_from_producer]
+        specs = [WindowSpec(m, self.cfg.seq_rank, self.cfg.seq_size) for m in self.metadata_from_producer]
+        self.splits = [s.splits for s in specs]
         self.engine = DeviceEngine(env, self.cfg, specs, self.batch_size)
         conn.attach(self.engine, pushers)
         for p in pushers:

@@ -77,14 +77,24 @@ class NullStream:
 class WindowSpec:
     """Geometry of one producer's window, derived from its ``on_init`` answer."""
 
-    def __init__(self, meta):
+    def __init__(self, meta, seq_rank: int = 0, seq_size: int = 1):
         self.nData = int(meta.nData)
-        self.nValues = int(meta.nValues)
+        self.window_values = int(meta.nValues)          # elements per row of the window / shard
         self.np_dtype = np.dtype(meta.dtype if meta.dtype is not None else np.float32)
+        self.window_bytes = self.window_values * self.np_dtype.itemsize
+        self.row_bytes = round_up(self.window_bytes, 16)
+        # what is delivered: the whole row, or this rank's column slice of it (sequence parallelism)
+        self.nValues, self.col_off = self.window_values, 0
+        if seq_size > 1:
+            if len(meta.splits) != 1 or self.window_values % seq_size:
+                raise ValueError("sequence sharding needs single-field rows whose length divides by seq_size")
+            self.nValues = self.window_values // seq_size
+            self.col_off = seq_rank * self.nValues * self.np_dtype.itemsize
+            if self.col_off % 16 or (self.nValues * self.np_dtype.itemsize) % 16:
+                raise ValueError("sequence shards must be multiples of 16 bytes")
         self.sample_bytes = self.nValues * self.np_dtype.itemsize
-        self.row_bytes = round_up(self.sample_bytes, 16)
         self.convert: Convert = meta.convert if meta.convert is not None else Convert.copy()
-        self.splits = tuple(int(s) for s in meta.splits)
+        self.splits = tuple(int(s) for s in meta.splits) if seq_size == 1 else (self.nValues,)
         self.var = bool(getattr(meta, "variable_length", False))
         if self.convert.mode == N.CVT_COPY:
             self.out_dtype = _TORCH_OF_NP[self.np_dtype]
@@ -119,7 +129,7 @@ class CpuGather:
         raw = np.empty((slots.size, sp.sample_bytes), dtype=np.uint8)
         for s in np.unique(src):
             m = src == s
-            raw[m] = self.shards[int(s)][row[m], :sp.sample_bytes]
+            raw[m] = self.shards[int(s)][row[m], sp.col_off:sp.col_off + sp.sample_bytes]
         cv = sp.convert
         if self.lengths is not None:
             self._run_padded(raw, self.lengths[src, row], out_raw)
@@ -251,7 +261,8 @@ class DeviceEngine:
             for s in specs:
                 self.plans.append(GatherPlan(self.sources, s.row_bytes, s.sample_bytes, s.convert,
                                              dst_row_bytes=ring_row, variant=config.gather_variant,
-                                             max_ctas=config.gather_max_ctas, tune=config.gather_tune))
+                                             max_ctas=config.gather_max_ctas, tune=config.gather_tune,
+                                             col_offset_bytes=s.col_off))
             self.h2d_copies = 0
             self.pinned = None
             if config.host_stage == "gather":
@@ -265,7 +276,8 @@ class DeviceEngine:
             for s in specs:
                 self.plans.append(GatherPlan(self.sources, s.row_bytes, s.sample_bytes, s.convert,
                                              dst_row_bytes=ring_row, variant=config.gather_variant,
-                                             max_ctas=config.gather_max_ctas, tune=config.gather_tune))
+                                             max_ctas=config.gather_max_ctas, tune=config.gather_tune,
+                                             col_offset_bytes=s.col_off))
         else:
             for k, s in enumerate(specs):
                 views = [self.heap.peer_buffer(where(g // self.P), f"shard{g % self.P}_i{g // self.P}").numpy(
@@ -296,12 +308,12 @@ class DeviceEngine:
     def alloc_window(self, k: int) -> np.ndarray:
         """Pinned host window handed to the user's post_init (reference: the MPI window)."""
         s = self.specs[k]
-        if self.host_resident and s.row_bytes == s.sample_bytes:
-            return self.shards[k].numpy(s.np_dtype, (s.nData, s.nValues))  # the window is the shard
+        if self.host_resident and s.row_bytes == s.window_bytes:
+            return self.shards[k].numpy(s.np_dtype, (s.nData, s.window_values))  # the window is the shard
         if self.cuda:
-            buf, _ = self.heap.alloc_pinned(f"window{k}", s.nData * s.sample_bytes)
-            return buf.numpy(s.np_dtype, (s.nData, s.nValues))
-        return np.zeros((s.nData, s.nValues), dtype=s.np_dtype)
+            buf, _ = self.heap.alloc_pinned(f"window{k}", s.nData * s.window_bytes)
+            return buf.numpy(s.np_dtype, (s.nData, s.window_values))
+        return np.zeros((s.nData, s.window_values), dtype=s.np_dtype)
 
     def load_shard(self, k: int, window: np.ndarray, stream=None) -> None:
         """Copy a filled host window into the HBM shard (row stride padded to 16 bytes)."""
@@ -312,15 +324,15 @@ class DeviceEngine:
         dst = self.shards[k].tensor(torch.uint8, (s.nData, s.row_bytes))
         st = stream or self.side
         if self.host_resident:
-            dst[:, :s.sample_bytes] = src
+            dst[:, :s.window_bytes] = src
         elif self.cuda:
             with torch.cuda.stream(st):
-                if s.row_bytes == s.sample_bytes:
+                if s.row_bytes == s.window_bytes:
                     dst.copy_(src, non_blocking=True)
                 else:
-                    dst[:, :s.sample_bytes].copy_(src, non_blocking=True)
+                    dst[:, :s.window_bytes].copy_(src, non_blocking=True)
         else:
-            dst[:, :s.sample_bytes] = src
+            dst[:, :s.window_bytes] = src
 
     def load_shard_from_device(self, k: int, data: torch.Tensor) -> None:
         """Fill shard k from a tensor that already lives on the device (synthetic benches)."""
@@ -328,7 +340,7 @@ class DeviceEngine:
         dst = self.shards[k].tensor(torch.uint8, (s.nData, s.row_bytes))
         src = data.reshape(s.nData, -1).view(torch.uint8)
         with torch.cuda.stream(self.side) if self.cuda else NullStream():
-            dst[:, :s.sample_bytes].copy_(src)
+            dst[:, :s.window_bytes].copy_(src)
 
     # -- variable-size windows ------------------------------------------------------------------------
     def set_lengths(self, k: int, lens_elems: np.ndarray) -> None:
@@ -523,7 +535,7 @@ class DeviceEngine:
         for s in self.specs:
             plan = GatherPlan(self.sources, s.row_bytes, s.sample_bytes, s.convert, dst_row_bytes=self.ring_row,
                               variant=self.cfg.gather_variant, max_ctas=self.cfg.gather_max_ctas,
-                              tune=self.cfg.gather_tune)
+                              tune=self.cfg.gather_tune, col_offset_bytes=s.col_off)
             plan.set_filter(self.me * self.P, (self.me + 1) * self.P)
             self.push_plans.append(plan)
 

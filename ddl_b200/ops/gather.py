@@ -139,7 +139,7 @@ class GatherPlan:
 
     def __init__(self, sources: SourceTable, row_bytes: int, sample_bytes: int, convert: Convert = Convert(),
                  dst_row_bytes: Optional[int] = None, variant: int = N.VARIANT_AUTO, max_ctas: int = 0,
-                 tune: int = 0):
+                 tune: int = 0, col_offset_bytes: int = 0):
         self.sources = sources
         self.convert = convert
         self.row_bytes = int(row_bytes)
@@ -162,6 +162,7 @@ class GatherPlan:
             d.bias[i] = convert.bias[i] if i < len(convert.bias) else 0.0
         d.pad_bits = convert.pad_bits()
         d.variant, d.max_ctas, d.tune = variant, max_ctas, tune
+        d.col_offset_bytes = int(col_offset_bytes)
         self._desc = d
         self._fn = N.lib().bddl_exchange_gather_collate
 

@@ -52,14 +52,14 @@ class StorageServer:
         heap.publish()
         for (i, k, pf, rank_global, s), shard in zip(work, shards):
             if cuda:
-                buf, _ = heap.alloc_pinned(f"window{k}_i{i}", s.nData * s.sample_bytes)
-                window = buf.numpy(s.np_dtype, (s.nData, s.nValues))
+                buf, _ = heap.alloc_pinned(f"window{k}_i{i}", s.nData * s.window_bytes)
+                window = buf.numpy(s.np_dtype, (s.nData, s.window_values))
             else:
-                window = np.zeros((s.nData, s.nValues), dtype=s.np_dtype)
+                window = np.zeros((s.nData, s.window_values), dtype=s.np_dtype)
             execute_callbacks("post_init", callbacks=[pf], compat=self.compat, rank_global=rank_global,
                               my_ary=window, n_instance=env.n_instances)
             dst = shard.tensor(torch.uint8, (s.nData, s.row_bytes))
-            dst[:, :s.sample_bytes].copy_(torch.from_numpy(window.reshape(s.nData, -1).view(np.uint8)))
+            dst[:, :s.window_bytes].copy_(torch.from_numpy(window.reshape(s.nData, -1).view(np.uint8)))
         if cuda:
             torch.cuda.synchronize(env.device)
         log.info("[%03d] storage rank holds %d shards for instances %s", me, len(work), hosted)

@@ -112,7 +112,7 @@ typedef struct bddl_gather_desc {
     int32_t max_ctas;                /* SM budget; 0 = one CTA per SM                             */
     int32_t filter_lo;               /* push form: only slots whose source is in [filter_lo,         */
     int32_t filter_hi;               /* filter_hi) are delivered (0,0 = deliver everything)          */
-    int32_t reserved;
+    int32_t col_offset_bytes;        /* deliver sample bytes [col_offset, col_offset + sample_bytes) (multiple of 16) */
     int32_t tune;                    /* stage ring per warp; convert: 0 = 16 warps x 3 x 4 KiB, 1 = 16 x 6 x 2 KiB, 2 = 8 x 3 x 8 KiB, 3 = 32 x 3 x 2 KiB */
 } bddl_gather_desc;
 

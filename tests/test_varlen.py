@@ -63,3 +63,41 @@ def test_variable_length_cpu():
 @pytest.mark.gpu
 def test_variable_length_gpu():
     run_case(None)
+
+
+class Tokens(ddl.ProducerFunctionSkeleton):
+    def on_init(self, **kw):
+        super().on_init(**kw)
+        return ddl.DataProducerOnInitReturn(256, 64, (256, 64), (64,), dtype=np.int32,
+                                            convert=ddl.Convert.widen_tokens(), shuffle_seed=self.rank_global)
+
+    def post_init(self, **kw):
+        kw["my_ary"][...] = np.arange(256 * 64, dtype=np.int32).reshape(256, 64)
+
+
+def run_sequence_shard(device):
+    """Context/sequence parallelism: each consumer receives only its column slice."""
+    for cp_rank in range(4):
+        @ddl.distributed_dataloader(n_instances=1, n_producers=1, device=device,
+                                    config=ddl.LoaderConfig(seq_rank=cp_rank, seq_size=4))
+        def main(env, conn):
+            loader = ddl.DistributedDataLoader(Tokens(), 32, conn, 1)
+            order = np.arange(256)
+            np.random.default_rng(1).shuffle(order)
+            for i, (x,) in enumerate(loader):
+                assert x.shape == (32, 16) and x.dtype == torch.int64
+                want = order[i * 32:(i + 1) * 32, None] * 64 + cp_rank * 16 + np.arange(16)[None, :]
+                assert np.array_equal(x.cpu().numpy(), want)
+                loader.mark(ddl.Marker.END_OF_BATCH)
+            loader.mark(ddl.Marker.END_OF_EPOCH)
+
+        main()
+
+
+def test_sequence_shard_cpu():
+    run_sequence_shard("cpu")
+
+
+@pytest.mark.gpu
+def test_sequence_shard_gpu():
+    run_sequence_shard(None)
