@@ -15,7 +15,6 @@ to the reference's own SendRecvReplaceGlobalShuffler.  No reference file is edit
 """
 import json
 import os
-import sys
 import time
 
 import numpy as np

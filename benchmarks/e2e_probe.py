@@ -1,7 +1,7 @@
-import sys, time, torch, numpy as np
-sys.path.insert(0, '/root/repo')
+import sys, time, torch
+sys.path.insert(0, __import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__))))
 import ddl_b200 as ddl
-from bench import make_producer, SAMPLE
+from bench import make_producer
 B, rows = 256, 4096
 for stage, sync, prio, ctas in (("pull", True, -1, 0), ("pull", True, 0, 0), ("pull", True, -1, 140), ("pull", True, 0, 140), ("pull", True, 0, 120)):
     cfg = ddl.LoaderConfig(metrics=False, ring_depth=3, residency="host", host_stage=stage, host_threads=8, fetch_priority=prio, gather_max_ctas=ctas)

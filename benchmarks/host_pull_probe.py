@@ -1,7 +1,6 @@
 """Zero-copy pull over PCIe: gather kernel reading a cudaHostAlloc'ed (torch pinned) shard."""
 import json, os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from ddl_b200 import _native as N
 from ddl_b200.ops import Convert, GatherPlan, SourceTable
 
 dev = torch.device("cuda:0")

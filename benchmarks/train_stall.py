@@ -11,13 +11,12 @@ import json
 import os
 import sys
 
-import numpy as np
 import torch
 import torch.nn.functional as F
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import ddl_b200 as ddl  # noqa: E402
-from bench import SAMPLE, make_producer  # noqa: E402
+from bench import make_producer  # noqa: E402
 from ddl_b200.models import resnet50  # noqa: E402
 
 

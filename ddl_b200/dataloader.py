@@ -24,9 +24,8 @@ import ctypes as C
 import logging
 import time
 from abc import ABC, abstractmethod
-from typing import Any, List, Optional, Tuple
+from typing import List, Optional, Tuple
 
-import numpy as np
 import torch
 
 from . import _native as N
@@ -34,7 +33,7 @@ from .config import LoaderConfig
 from .connection import Connection
 from .datapusher import DevicePusher
 from .datasetwrapper import ProducerFunctionSkeleton
-from .engine import DeviceEngine, NullEvent, NullStream, WindowSpec
+from .engine import DeviceEngine, NullStream, WindowSpec
 from .ops.gather import GatherPlan, SourceTable, make_slot
 from .types import Marker, MetaData_Consumer_To_Producer, MetaData_Producer_To_Consumer
 from .utils import for_all_methods, with_logging
@@ -405,6 +404,13 @@ class DistributedDataLoader(DistributedDataloaderABC):
     def trace_summary(self) -> dict:
         """Device-time statistics per loader stage (needs ``LoaderConfig(trace=True)``)."""
         return self.engine.tracer.summary() if self.engine is not None else {}
+
+    def __enter__(self) -> "DistributedDataLoader":
+        return self
+
+    def __exit__(self, exc_type, exc, tb) -> bool:
+        self.close()  # also on an exception in the training loop, so producers and peers are released
+        return False
 
     def close(self) -> None:
         """Early shutdown (the reference can only stop by running out of epochs)."""
