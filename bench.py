@@ -188,7 +188,8 @@ def run_ours(args) -> dict:
 
     cfg = ddl.LoaderConfig.from_env(metrics=False, ring_depth=args.ring, gather_variant=args.variant,
                                     gather_tune=args.tune, prefetch_depth=args.prefetch_depth,
-                                    fetch_streams=args.fetch_streams, exchange=args.exchange)
+                                    fetch_streams=args.fetch_streams, exchange=args.exchange,
+                                    gather_max_ctas=args.max_ctas)
     if not args.e2e_only:
         ddl.distributed_dataloader(body, n_instances="world", n_producers=1, config=cfg)()
     else:
@@ -249,6 +250,7 @@ def main():
     ap.add_argument("--tune", type=int, default=0)
     ap.add_argument("--prefetch-depth", type=int, default=3)
     ap.add_argument("--fetch-streams", type=int, default=3)
+    ap.add_argument("--max-ctas", type=int, default=0)
     ap.add_argument("--exchange", default="pull", choices=["pull", "push"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-only", action="store_true")

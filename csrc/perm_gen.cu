@@ -8,12 +8,12 @@
 // is one warp per table that walks the 32-bit draw stream 32 draws at a time:
 //   * each lane owns one draw of the batch (PCG64 is an LCG: lane l keeps its own state and
 //     jumps 16 outputs per batch, so the raw stream is produced in parallel);
-//   * accept/reject of all 32 draws is resolved with one ballot when no draw lands in the
-//     32-wide ambiguous band under the running index (probability ~1024/i per batch);
+//   * whether a draw is accepted depends only on how many earlier draws of the batch were, so
+//     accept/reject of all 32 draws is a fixed point found with a few ballots (two in practice);
 //   * the accepted swaps of a batch touch disjoint entries unless two draws collide
-//     (__match_any_sync), so they are applied as 32 parallel swaps;
-//   * any batch that is ambiguous, collides, crosses a power-of-two mask boundary or reaches
-//     the end of the table replays its 32 draws one at a time (exact sequential semantics).
+//     (__match_any_sync) or a target falls into the batch's own index window; then they are
+//     applied as up to 32 parallel swaps, otherwise one at a time in order;
+//   * the last 64 entries replay their draws one at a time (exact end-of-stream accounting).
 // Table accesses go through L2 (ld/st .cg) so that lanes always see each other's swaps.  Once
 // the running index drops below kSmemEntries the live prefix of the table is pulled into shared
 // memory and finished there: small indices are where batches fall back to the sequential replay
@@ -100,38 +100,52 @@ __global__ void __launch_bounds__(32) perm_gen_kernel(uint64_t* tables, int64_t 
             }
             const uint64_t out = pcg_output(st);
             const uint32_t d = (lane & 1) ? (uint32_t)(out >> 32) : (uint32_t)out;
-            const uint64_t mask = bddl_mask_for((uint64_t)i);
-            const uint64_t seg_lo = (mask >> 1) + 1;  // smallest index sharing this mask
-            // Fast path needs every index of the batch (i .. i-31) to share one mask.
-            bool fast = (uint64_t)i >= seg_lo + 32;
-            const uint64_t v = (uint64_t)d & mask;
-            // v <= i-32 is accepted whatever index the lane ends up with, and then lies
-            // strictly below every index of the batch; v > i is rejected; in between the
-            // outcome depends on the accepts of earlier lanes.
-            const bool accept = v + 32 <= (uint64_t)i;
-            if (fast) {
-                const bool ambiguous = !accept && v <= (uint64_t)i;
-                fast = !__any_sync(0xffffffffu, ambiguous);
-            }
-            if (fast) {
-                const unsigned acc = __ballot_sync(0xffffffffu, accept);
-                bool collide = false;
-                if (accept) collide = __match_any_sync(acc, v) != (1u << lane);
-                fast = !__any_sync(0xffffffffu, collide);
-                if (fast) {
-                    if (accept) {
-                        const int64_t my_i = i - (int64_t)__popc(acc & ((1u << lane) - 1u));
-                        const uint64_t a = ld(my_i), b = ld((int64_t)v);
-                        st_(my_i, b);
+            if (i >= 64) {
+                // All 32 draws of the batch are consumed.  Which of them are accepted depends only
+                // on how many earlier lanes were accepted, so iterate that count to its (unique)
+                // fixed point: lane t is exact after t+1 rounds, in practice two rounds suffice.
+                const unsigned lt = (1u << lane) - 1u;
+                unsigned acc = 0;
+                int64_t idx;
+                uint64_t v;
+                for (;;) {
+                    idx = i - (int64_t)__popc(acc & lt);
+                    v = (uint64_t)d & (~0ULL >> __clzll((long long)idx));  // numpy's mask for this index
+                    const unsigned now = __ballot_sync(0xffffffffu, v <= (uint64_t)idx);
+                    if (now == acc) break;
+                    acc = now;
+                }
+                const bool mine = (acc >> lane) & 1u;
+                // The accepted swaps commute unless two of them share a target or a target lies
+                // inside the batch's own index window.
+                bool clash = false;
+                if (mine)
+                    clash = __match_any_sync(acc, v) != (1u << lane) || (v + 31 >= (uint64_t)i && v != (uint64_t)idx);
+                if (!__any_sync(0xffffffffu, clash)) {
+                    if (mine && v != (uint64_t)idx) {
+                        const uint64_t a = ld(idx), b = ld((int64_t)v);
+                        st_(idx, b);
                         st_((int64_t)v, a);
                     }
                     __syncwarp();
-                    i -= (int64_t)__popc(acc);
-                    draws += 32;
-                    base = shfl_u128(st, 31);  // state after 16 outputs
-                    st = u128_add(u128_mul(j16m, st), j16p);
-                    continue;
+                } else {
+                    for (unsigned rem = acc; rem; rem &= rem - 1) {  // in order, one swap at a time
+                        const int t = __ffs(rem) - 1;
+                        const int64_t it = __shfl_sync(0xffffffffu, idx, t);
+                        const int64_t jt = (int64_t)__shfl_sync(0xffffffffu, v, t);
+                        if (lane == 0) {
+                            const uint64_t a = ld(it), b = ld(jt);
+                            st_(it, b);
+                            st_(jt, a);
+                        }
+                        __syncwarp();
+                    }
                 }
+                i -= (int64_t)__popc(acc);
+                draws += 32;
+                base = shfl_u128(st, 31);  // state after 16 outputs
+                st = u128_add(u128_mul(j16m, st), j16p);
+                continue;
             }
             // Replay: consume this batch's draws in order with the exact sequential rule.
             int used = 0;
