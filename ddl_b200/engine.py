@@ -398,7 +398,7 @@ class DeviceEngine:
             if self._barrier_tensor is None:
                 self._barrier_tensor = torch.zeros(1, device=self.device)
             with torch.cuda.stream(self.side):
-                dist.all_reduce(self._barrier_tensor, group=self.env.consumer_group)
+                dist.all_reduce(self._barrier_tensor, group=self.env.loader_group or self.env.consumer_group)
         elif mode == "flags":
             self._flag_barrier()
         else:

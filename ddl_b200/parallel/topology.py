@@ -49,6 +49,7 @@ class Env:
     n_producers: int = 1
     device: torch.device = torch.device("cpu")
     consumer_group: Any = None  # torch ProcessGroup of the consumers (the DDP world)
+    loader_group: Any = None    # private ProcessGroup of the consumers for the loader's own stream barriers
     n_storage: int = 0          # dedicated storage ranks (GPUs that only hold shards), device transport
     is_storage: bool = False
 
@@ -108,19 +109,20 @@ def _init_env_with_storage(n_instances, n_storage, world, n_producers, device, m
     device = torch.device(device)
     if device.type == "cuda":
         torch.cuda.set_device(device)
-    group = None
+    group = private = None
     try:
         import torch.distributed as dist
 
         if make_consumer_group and dist.is_initialized():
             group = dist.new_group(list(range(n_instances)))
+            private = dist.new_group(list(range(n_instances)))
     except Exception as e:
         log.warning("could not create the consumer process group: %s", e)
     producers = int(n_producers if n_producers is not None else os.environ.get("DDL_B200_PRODUCERS", "1"))
     return Env(comm_global=comm_global, comm_per_gpu=own, comm_per_gpu_shm=own, comm_nth_pusher=role,
                color=rank if not is_storage else rank - n_instances, color_nth_pusher=0, n_instances=n_instances,
                world=world, transport="device", n_producers=producers, device=device, consumer_group=group,
-               n_storage=n_storage, is_storage=is_storage)
+               n_storage=n_storage, is_storage=is_storage, loader_group=private)
 
 
 def init_env(n_instances: int = 1, world: Optional[World] = None, n_producers: Optional[int] = None,
@@ -166,20 +168,24 @@ def init_env(n_instances: int = 1, world: Optional[World] = None, n_producers: O
     if device.type == "cuda":
         torch.cuda.set_device(device)
 
-    consumer_group = None
+    consumer_group = loader_group = None
     try:
         import torch.distributed as dist
 
         if make_consumer_group and dist.is_initialized() and n_instances > 1:
             consumers: List[int] = [i * group_size for i in range(n_instances)]
             consumer_group = dist.group.WORLD if transport == "device" else dist.new_group(consumers)
+            if transport == "device":
+                # the loader's stream barriers must never interleave with the user's collectives
+                # (DDP buckets) on one communicator: give them a communicator of their own
+                loader_group = dist.new_group(consumers)
     except Exception as e:  # a missing DDP group is not fatal for the loader itself
         log.warning("could not create the consumer process group: %s", e)
 
     return Env(comm_global=comm_global, comm_per_gpu=comm_per_gpu, comm_per_gpu_shm=comm_per_gpu_shm,
                comm_nth_pusher=comm_nth_pusher, color=color, color_nth_pusher=color_nth, n_instances=n_instances,
                world=world, transport=transport, n_producers=producers, device=device,
-               consumer_group=consumer_group)
+               consumer_group=consumer_group, loader_group=loader_group)
 
 
 def instances_from_environment(default: int = 1) -> int:
