@@ -50,6 +50,9 @@ class LoaderConfig:
     seq_size: int = 1
     timeout_s: float = 600.0       # bounded waits: a dead producer raises instead of hanging
     metrics: bool = True
+    # integrity mode (the stand-in for a race detector): every batch is assembled a
+    # second time by the independent LDG form of the kernel and the two fingerprints are compared
+    verify: bool = False
     trace: bool = False            # CUDA-event timing of every loader stage
     fence_every_batch: bool = False
 

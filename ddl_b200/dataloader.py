@@ -83,6 +83,7 @@ class DistributedDataLoader(DistributedDataloaderABC):
         self._finalized = False
         self._lend_seq = 0
         self._pref: dict = {}
+        self._verify_pending: list = []
         self._cur_slot = -1
         self._next_slot = 0
 
@@ -266,6 +267,9 @@ class DistributedDataLoader(DistributedDataloaderABC):
                     eng.push_step(k, self.connection.pushers[k].lent_buf, b * B, slot, stream)
                 else:
                     eng.gather(k, self.connection.pushers[k].lent_buf, b * B, slot, stream=stream)
+            if self.cfg.verify and eng.cuda and not eng.push and eng.stage is None:
+                self._verify_pending.append((b, eng.verify_batch(k, self.connection.pushers[k].lent_buf, b * B,
+                                                                 slot, stream)))
             ev = eng.event()
             if eng.cuda:
                 ev.record(stream)
@@ -320,7 +324,17 @@ class DistributedDataLoader(DistributedDataloaderABC):
             self.target_rank = 1
         self._len = self.batches_per_window[self.target_rank - 1]
 
+    def _check_verified(self) -> None:
+        pending, self._verify_pending = self._verify_pending, []
+        for b, pair in pending:
+            x, y = pair.tolist()  # synchronises: integrity mode is a debugging aid
+            if x != y:
+                raise RuntimeError(f"integrity check failed for batch {b}: TMA and LDG forms of "
+                                   f"exchange_gather_collate disagree ({x:#x} != {y:#x})")
+
     def _on_batch_end(self) -> None:
+        if self._verify_pending:
+            self._check_verified()
         if self._cur_slot >= 0 and not isinstance(self.main, NullStream):
             ev = self._consumed[self._cur_slot]
             if ev is None:

@@ -573,6 +573,32 @@ class DeviceEngine:
                                          self._use[ring_slot], 0, C.c_void_p(stream.cuda_stream)))
         self.launches += 1
 
+    # -- integrity mode -----------------------------------------------------------------------------------
+    def verify_batch(self, k: int, buf: int, first_row: int, ring_slot: int, stream) -> torch.Tensor:
+        """Assemble the same batch again with the LDG form into a scratch buffer and return the
+        two fingerprints ([2] int64 on the device); they must be equal."""
+        from .ops.checksum import BatchChecksum
+
+        s = self.specs[k]
+        if not hasattr(self, "_verify"):
+            self._verify = {}
+        if k not in self._verify:
+            base = self.plans[k]
+            plan = GatherPlan(base.sources, s.row_bytes if not s.var else 0, s.sample_bytes, s.convert,
+                              dst_row_bytes=self.ring_row, variant=N.VARIANT_LDG, col_offset_bytes=s.col_off)
+            scratch = torch.zeros((self.B, self.ring_row), dtype=torch.uint8, device=self.device)
+            payload = max(8, s.out_sample_bytes // 8 * 8)
+            self._verify[k] = (plan, scratch, BatchChecksum(self.device, self.B, payload),
+                               BatchChecksum(self.device, self.B, payload), payload)
+        plan, scratch, ca, cb, payload = self._verify[k]
+        plan.run_ptr(self.table_ptr(k, buf, first_row), scratch.data_ptr(), self.B, stream.cuda_stream)
+        a = ca.run(self.ring[ring_slot], payload, stream=stream)
+        b = cb.run(scratch, payload, stream=stream)
+        with torch.cuda.stream(stream):
+            out = torch.cat([a, b])
+        self.launches += 3
+        return out
+
     def on_lend(self, k: int, buf: int) -> None:
         """Called when the consumer borrows window k: host staging needs the table on the host."""
         if self.stage is not None:

@@ -83,6 +83,10 @@ def test_checkpoint_resume_on_gpu():
     tc.run_resume_case(None)
 
 
+def test_integrity_mode_cross_checks_kernel_forms():
+    _run(ddl.LoaderConfig(verify=True, ring_depth=3, prefetch_depth=2), v=64)
+
+
 def test_tracing_reports_device_time_per_stage():
     got = {}
 
