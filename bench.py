@@ -181,10 +181,12 @@ def run_ours(args) -> dict:
                                            env.color, env.n_instances)
         ms, launches, clocks = timed_loop(loader, env, args.steps, args.warmup, e2e=False)
         # numerics spot check of one delivered batch against the fp32 PyTorch statement
+        remote = max(env.comm_global.allgather_obj(loader.remote_fraction()))
         (x,) = loader[0]
         ok = bool(torch.isfinite(x.float()).all().item()) and x.shape == (B, SAMPLE) and x.dtype == torch.bfloat16
         loader.close()
-        result.update(ms=ms, launches=launches, clocks=clocks, ok=ok, n=env.n_instances, rank=env.comm_global.rank)
+        result.update(ms=ms, launches=launches, clocks=clocks, ok=ok, n=env.n_instances, rank=env.comm_global.rank,
+                      remote=remote)
 
     cfg = ddl.LoaderConfig.from_env(metrics=False, ring_depth=args.ring, gather_variant=args.variant,
                                     gather_tune=args.tune, prefetch_depth=args.prefetch_depth,
@@ -193,7 +195,7 @@ def run_ours(args) -> dict:
     if not args.e2e_only:
         ddl.distributed_dataloader(body, n_instances="world", n_producers=1, config=cfg)()
     else:
-        result.update(ms=1.0, launches=0, clocks=None, ok=True, rank=int(os.environ.get("RANK", "0")))
+        result.update(ms=1.0, launches=0, clocks=None, ok=True, rank=int(os.environ.get("RANK", "0")), remote=0.0)
 
     e2e = None
     if not args.no_e2e:
@@ -230,6 +232,10 @@ def run_ours(args) -> dict:
                    "rows_per_gpu": args.rows, "fraction_exchange": args.fraction, "exchange": args.exchange,
                    "l2": "inputs larger than L2 (shard %.1f GB per GPU, every row read once per epoch)"
                          % (args.rows * SAMPLE / 1e9)},
+        "exchange": {"remote_fraction": round(result.get("remote", 0.0), 4),
+                     "nvlink_in_gbs_per_gpu": round(result.get("remote", 0.0) * args.batch * SAMPLE / (ms_per_step * 1e6), 1),
+                     "frac_of_900_nominal": round(result.get("remote", 0.0) * args.batch * SAMPLE / (ms_per_step * 1e6) / 900, 3),
+                     "frac_of_770_measured": round(result.get("remote", 0.0) * args.batch * SAMPLE / (ms_per_step * 1e6) / 770, 3)},
         "clocks": result["clocks"], "e2e": e2e, "gpu_launches": int(result["launches"]),
         "numerics_ok": result["ok"], "impl": "ddl_b200",
     }

@@ -395,6 +395,16 @@ class DistributedDataLoader(DistributedDataloaderABC):
         b = self._cur_batch
         return self.engine.batch_lengths(k, self.connection.pushers[k].lent_buf, b * self.batch_size, self.batch_size)
 
+    def remote_fraction(self) -> float:
+        """Share of the current window's samples that live on another GPU (what crosses NVLink)."""
+        if self.transport != "device":
+            return 0.0
+        eng, k = self.engine, self.target_rank - 1
+        tbl = eng.table(k, self.connection.pushers[k].lent_buf)
+        owner = (tbl >> 48) // eng.P
+        where = owner if not eng.remote_storage else owner * 0 - 1
+        return float((where != eng.me).float().mean().item())
+
     def batch_checksum(self) -> torch.Tensor:
         """Enqueue (on the current stream) the 64-bit fingerprint of the batch handed out last and
         return the one-element device tensor that will hold it: a cheap per-step result to read
