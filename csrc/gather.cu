@@ -635,3 +635,14 @@ extern "C" int bddl_exchange_gather_collate(const bddl_gather_desc* d, void* str
             return launch_mode<BDDL_CVT_I32_I64, false>(d, p, tma, st);
     }
 }
+
+// One loader step in one call: [wait until the ring slot is free] -> assemble the batch ->
+// [record that it is done].  Either event may be null.
+extern "C" int bddl_gather_step(const bddl_gather_desc* d, void* stream, void* wait_event, void* record_event) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (wait_event) BDDL_CUDA(cudaStreamWaitEvent(st, (cudaEvent_t)wait_event, 0));
+    int rc = bddl_exchange_gather_collate(d, stream);
+    if (rc) return rc;
+    if (record_event) BDDL_CUDA(cudaEventRecord((cudaEvent_t)record_event, st));
+    return 0;
+}

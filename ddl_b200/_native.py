@@ -115,6 +115,12 @@ def _declare(lib: C.CDLL) -> None:
         "bddl_memset_async": (C.c_int, [vp, C.c_int, sz, vp]),
         "bddl_memcpy_async": (C.c_int, [vp, vp, sz, i32, vp]),
         "bddl_stream_synchronize": (C.c_int, [vp]),
+        "bddl_event_create": (C.c_int, [P(vp)]),
+        "bddl_event_destroy": (C.c_int, [vp]),
+        "bddl_event_record": (C.c_int, [vp, vp]),
+        "bddl_stream_wait_event": (C.c_int, [vp, vp]),
+        "bddl_event_synchronize": (C.c_int, [vp]),
+        "bddl_gather_step": (C.c_int, [P(GatherDesc), vp, vp, vp]),
         "bddl_ipc_get_handle": (C.c_int, [vp, vp]),
         "bddl_ipc_open_handle": (C.c_int, [vp, P(vp)]),
         "bddl_ipc_close_handle": (C.c_int, [vp]),

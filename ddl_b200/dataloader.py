@@ -33,7 +33,7 @@ from .config import LoaderConfig
 from .connection import Connection
 from .datapusher import DevicePusher
 from .datasetwrapper import ProducerFunctionSkeleton
-from .engine import DeviceEngine, NullStream, WindowSpec
+from .engine import DeviceEngine, NullStream, WindowSpec, stream_wait
 from .ops.gather import GatherPlan, SourceTable, make_slot
 from .types import Marker, MetaData_Consumer_To_Producer, MetaData_Producer_To_Consumer
 from .utils import for_all_methods, with_logging
@@ -83,6 +83,7 @@ class DistributedDataLoader(DistributedDataloaderABC):
         self._finalized = False
         self._lend_seq = 0
         self._pref: dict = {}
+        self._fast = False
         self._verify_pending: list = []
         self._cur_slot = -1
         self._next_slot = 0
@@ -144,7 +145,13 @@ class DistributedDataLoader(DistributedDataloaderABC):
         eng.heap_comm.barrier()  # every shard is resident before anyone's kernel may pull from it
         for p in pushers:
             p.start()
-        self._consumed = [None] * eng.ring_depth
+        self._consumed = [eng.event() if eng.cuda else None for _ in range(eng.ring_depth)]
+        self._done = [eng.event() for _ in range(eng.ring_depth)]
+        self._ring_ptr = [r.data_ptr() for r in eng.ring]
+        # the one-call hot path covers the product's main configuration; everything else
+        # (push form, host staging, tracing, integrity mode, metrics) takes the general path
+        self._fast = (eng.cuda and not eng.push and eng.stage is None and not self.cfg.trace
+                      and not self.cfg.verify)
         self._views = {}
         self.main = eng.main
         self.fetch = eng.fetch
@@ -233,7 +240,7 @@ class DistributedDataLoader(DistributedDataloaderABC):
             t0 = time.perf_counter()
             ev.synchronize()
             self.metrics.stall(time.perf_counter() - t0)
-        self.main.wait_event(ev)
+        stream_wait(self.main, ev)
         self._cur_slot, self._cur_batch = slot, b
         if self.cfg.prefetch:
             for d in range(1, self.cfg.prefetch_depth + 1):
@@ -256,21 +263,34 @@ class DistributedDataLoader(DistributedDataloaderABC):
         slot = self._next_slot
         self._next_slot = (slot + 1) % len(self._consumed)
         stream = self.fetch_streams[slot % len(self.fetch_streams)]
+        B = self.batch_size
+        if self._fast:
+            # hot path: wait for the slot, assemble, record done -- one native call
+            eng = self.engine
+            done = self._done[slot]
+            eng.plans[k].step_ptr(eng.table_ptr(k, self.connection.pushers[k].lent_buf, b * B), self._ring_ptr[slot],
+                                  B, stream.cuda_stream, self._consumed[slot].handle, done.handle)
+            eng.launches += 1
+            if self.metrics.enabled:
+                s = eng.specs[k]
+                self.metrics.batch(B, B * s.sample_bytes, B * s.out_sample_bytes)
+            return slot, done
         done = self._consumed[slot]
         if done is not None:
-            stream.wait_event(done)  # the training stream has finished with this ring slot
-        B = self.batch_size
+            stream_wait(stream, done)  # the training stream has finished with this ring slot
         if self.transport == "device":
             eng = self.engine
-            with eng.tracer.span("gather", stream):
-                if eng.push:
-                    eng.push_step(k, self.connection.pushers[k].lent_buf, b * B, slot, stream)
-                else:
+            if eng.tracer.enabled:
+                with eng.tracer.span("gather", stream):
                     eng.gather(k, self.connection.pushers[k].lent_buf, b * B, slot, stream=stream)
+            elif eng.push:
+                eng.push_step(k, self.connection.pushers[k].lent_buf, b * B, slot, stream)
+            else:
+                eng.gather(k, self.connection.pushers[k].lent_buf, b * B, slot, stream=stream)
             if self.cfg.verify and eng.cuda and not eng.push and eng.stage is None:
                 self._verify_pending.append((b, eng.verify_batch(k, self.connection.pushers[k].lent_buf, b * B,
                                                                  slot, stream)))
-            ev = eng.event()
+            ev = self._done[slot]
             if eng.cuda:
                 ev.record(stream)
             s = eng.specs[k]

@@ -236,8 +236,11 @@ class DevicePusher:
     def produce(self) -> None:
         eng, k = self.engine, self.k
         for ev in self._returned_ev or ():
-            eng.side.wait_event(ev)  # the buffer about to be rewritten is no longer read
-        with eng.tracer.span(f"produce.window{k + 1}", eng.side):
+            eng.wait(eng.side, ev)  # the buffer about to be rewritten is no longer read
+        if eng.tracer.enabled:
+            with eng.tracer.span(f"produce.window{k + 1}", eng.side):
+                self._produce_body(eng, k)
+        else:
             self._produce_body(eng, k)
         ev = eng.event()
         ev.record(eng.side) if eng.cuda else None
@@ -284,7 +287,7 @@ class DevicePusher:
         buf, ev = self._ready
         eng = self.engine
         for st in eng.fetch_streams:
-            st.wait_event(ev)
+            eng.wait(st, ev)
         self.lent_buf = buf
         eng.on_lend(self.k, buf)
         if self.run_ahead and not self._stopped:

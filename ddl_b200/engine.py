@@ -41,6 +41,39 @@ _TORCH_OF_NP = {np.dtype(np.float32): torch.float32, np.dtype(np.uint8): torch.u
                 np.dtype(np.float64): torch.float64, np.dtype(np.int16): torch.int16, np.dtype(np.int8): torch.int8}
 
 
+class NativeEvent:
+    """A raw cudaEvent_t (timing disabled) driven through the native library: recording and
+    waiting cost one ctypes call each, and ``bddl_gather_step`` can take the handles directly."""
+
+    __slots__ = ("handle",)
+
+    def __init__(self):
+        h = C.c_void_p()
+        N.check(N.lib().bddl_event_create(C.byref(h)))
+        self.handle = h.value
+
+    def record(self, stream=None) -> None:
+        s = stream if stream is not None else torch.cuda.current_stream()
+        N.lib().bddl_event_record(self.handle, s.cuda_stream)
+
+    def synchronize(self) -> None:
+        N.check(N.lib().bddl_event_synchronize(self.handle))
+
+    def __del__(self):
+        try:
+            N.lib().bddl_event_destroy(self.handle)
+        except Exception:
+            pass
+
+
+def stream_wait(stream, ev) -> None:
+    """``stream`` waits for ``ev``: native, torch or null events alike."""
+    if isinstance(ev, NativeEvent):
+        N.lib().bddl_stream_wait_event(stream.cuda_stream, ev.handle)
+    elif ev is not None:
+        stream.wait_event(ev)
+
+
 class NullEvent:
     def record(self, stream=None):
         pass
@@ -293,7 +326,11 @@ class DeviceEngine:
 
     # -- helpers --------------------------------------------------------------------------------
     def event(self):
-        return torch.cuda.Event(enable_timing=self.cfg.trace) if self.cuda else NullEvent()
+        return NativeEvent() if self.cuda else NullEvent()
+
+    @staticmethod
+    def wait(stream, ev) -> None:
+        stream_wait(stream, ev)
 
     def source_id(self, k: int, instance: Optional[int] = None) -> int:
         return (self.me if instance is None else instance) * self.P + k

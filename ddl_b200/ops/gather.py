@@ -165,6 +165,7 @@ class GatherPlan:
         d.col_offset_bytes = int(col_offset_bytes)
         self._desc = d
         self._fn = N.lib().bddl_exchange_gather_collate
+        self._step = N.lib().bddl_gather_step
 
     def set_filter(self, lo: int, hi: int) -> None:
         """Push form: deliver only slots whose source id is in [lo, hi) (0, 0 = everything)."""
@@ -197,6 +198,15 @@ class GatherPlan:
         d.n_samples = n
         s = stream if stream is not None else torch.cuda.current_stream(self.sources.device)
         N.check(self._fn(C.byref(d), C.c_void_p(s.cuda_stream)))
+
+    def step_ptr(self, slots_ptr: int, dst_ptr: int, n_samples: int, stream_ptr: int, wait_event: int,
+                 record_event: int) -> None:
+        """[wait for `wait_event`] -> launch -> [record `record_event`] in one native call."""
+        d = self._desc
+        d.d_slots, d.d_dst, d.n_samples = slots_ptr, dst_ptr, n_samples
+        rc = self._step(C.byref(d), stream_ptr, wait_event, record_event)
+        if rc:
+            N.check(rc)
 
     def run_ptr(self, slots_ptr: int, dst_ptr: int, n_samples: int, stream_ptr: int) -> None:
         """Lowest-overhead launch for the per-step hot loop (raw addresses)."""

@@ -117,6 +117,8 @@ typedef struct bddl_gather_desc {
 } bddl_gather_desc;
 
 int bddl_exchange_gather_collate(const bddl_gather_desc* desc, void* stream);
+/* One loader step in one call: [cudaStreamWaitEvent(wait_event)] -> assemble -> [cudaEventRecord(record_event)]. */
+int bddl_gather_step(const bddl_gather_desc* desc, void* stream, void* wait_event, void* record_event);
 /* Number of kernels this library has launched in this process (for gpu_launches accounting). */
 int64_t bddl_launch_count(void);
 
@@ -150,6 +152,11 @@ int bddl_free(void* p);
 int bddl_memset_async(void* p, int value, size_t bytes, void* stream);
 int bddl_memcpy_async(void* dst, const void* src, size_t bytes, int32_t kind, void* stream);
 int bddl_stream_synchronize(void* stream);
+int bddl_event_create(void** ev);               /* cudaEventDisableTiming */
+int bddl_event_destroy(void* ev);
+int bddl_event_record(void* ev, void* stream);
+int bddl_stream_wait_event(void* stream, void* ev);
+int bddl_event_synchronize(void* ev);
 int bddl_ipc_get_handle(void* p, uint8_t handle[64]);
 int bddl_ipc_open_handle(const uint8_t handle[64], void** p);
 int bddl_ipc_close_handle(void* p);
