@@ -177,24 +177,75 @@ class Comm:
 
     # -- bulk (the reference's Sendrecv_replace, ddl/shuffle.py:95-108) -----------------------------
     def sendrecv_replace(self, array: np.ndarray, dest: int, source: int, sendtag: int = 0, recvtag: int = 0) -> None:
-        """Send ``array`` to ``dest`` and overwrite it with what ``source`` sends (in place)."""
+        """Send ``array`` to ``dest`` and overwrite it with what ``source`` sends (in place).
+
+        Payloads of peers on the same node travel through a POSIX shared-memory segment (one
+        memcpy in, one out); only its name goes through the store.  Peers on other nodes, and
+        tiny payloads, use store values in chunks."""
         if not array.flags.c_contiguous:
             raise ValueError("sendrecv_replace needs a C-contiguous array")
         buf = array.reshape(-1).view(np.uint8)
+        nbytes = int(buf.size)
         seq_s = self._next("bs", self.rank, dest, sendtag)
-        n_chunks = max(1, (buf.size + _CHUNK - 1) // _CHUNK)
         base_s = f"{self.name}/b/{self.rank}>{dest}/{sendtag}/{seq_s}"
-        for i in range(n_chunks):
-            self.store.set(f"{base_s}/{i}", buf[i * _CHUNK:(i + 1) * _CHUNK].tobytes())
         seq_r = self._next("br", source, self.rank, recvtag)
         base_r = f"{self.name}/b/{source}>{self.rank}/{recvtag}/{seq_r}"
-        for i in range(n_chunks):
-            data = self._get(f"{base_r}/{i}")
-            chunk = np.frombuffer(data, dtype=np.uint8)
-            if chunk.size != buf[i * _CHUNK:(i + 1) * _CHUNK].size:
-                raise ValueError(f"{self.name}: sendrecv_replace size mismatch with rank {source}")
-            buf[i * _CHUNK:(i + 1) * _CHUNK] = chunk
-            self._delete(f"{base_r}/{i}")
+        via_shm = nbytes >= (1 << 16) and self._same_host(dest)
+        seg = None
+        if via_shm:
+            import ctypes as C
+
+            from .. import _native as N
+
+            name = "/bddl_sr_%x" % (abs(hash((base_s, os.getpid(), time.monotonic_ns()))) % (1 << 60))
+            p = C.c_void_p()
+            N.check(N.lib().bddl_shm_create(name.encode(), nbytes, C.byref(p)))
+            C.memmove(p.value, buf.ctypes.data, nbytes)
+            seg = (name, p.value)
+            self.store.set(base_s, pickle.dumps(("shm", name, nbytes)))
+        else:
+            n_chunks = max(1, (nbytes + _CHUNK - 1) // _CHUNK)
+            self.store.set(base_s, pickle.dumps(("store", n_chunks, nbytes)))
+            for i in range(n_chunks):
+                self.store.set(f"{base_s}/{i}", buf[i * _CHUNK:(i + 1) * _CHUNK].tobytes())
+        kind, a, peer_bytes = pickle.loads(self._get(base_r))
+        self._delete(base_r)
+        if peer_bytes != nbytes:
+            raise ValueError(f"{self.name}: sendrecv_replace size mismatch with rank {source} "
+                             f"({peer_bytes} != {nbytes} bytes)")
+        if kind == "shm":
+            import ctypes as C
+
+            from .. import _native as N
+
+            q = C.c_void_p()
+            N.check(N.lib().bddl_shm_attach(a.encode(), nbytes, C.byref(q)))
+            C.memmove(buf.ctypes.data, q.value, nbytes)
+            N.lib().bddl_shm_detach(q, nbytes)
+        else:
+            for i in range(a):
+                data = self._get(f"{base_r}/{i}")
+                buf[i * _CHUNK:(i + 1) * _CHUNK] = np.frombuffer(data, dtype=np.uint8)
+                self._delete(f"{base_r}/{i}")
+        self.store.set(base_r + "/ack", b"1")
+        self._get(base_s + "/ack")  # my payload has been copied out
+        self._delete(base_s + "/ack")
+        if seg is not None:
+            import ctypes as C
+
+            from .. import _native as N
+
+            N.lib().bddl_shm_detach(C.c_void_p(seg[1]), nbytes)
+            N.lib().bddl_shm_unlink(seg[0].encode())
+
+    def _same_host(self, peer: int) -> bool:
+        if not hasattr(self, "_hosts"):
+            self._hosts = None
+        if self._hosts is None:
+            # filled lazily by the first collective use; sendrecv_replace is always called by the
+            # whole group in the reference's exchange, so a collective here is safe
+            self._hosts = self.hostnames()
+        return self._hosts[peer] == self._hosts[self.rank]
 
     Sendrecv_replace = sendrecv_replace
 

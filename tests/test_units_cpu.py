@@ -118,6 +118,19 @@ def test_comm_point_to_point_fifo_and_collectives():
     assert all(run_ranks(4, body))
 
 
+def test_sendrecv_replace_bulk_goes_through_shared_memory():
+    def body(w):
+        c = w.comm
+        nxt, prv = (c.rank + 1) % c.size, (c.rank - 1) % c.size
+        a = np.full((512, 1024), c.rank, dtype=np.float32)  # 2 MiB: the shared-memory path
+        a[:, 0] = np.arange(512)
+        c.sendrecv_replace(a, dest=nxt, source=prv, sendtag=51, recvtag=51)
+        assert (a[:, 1:] == prv).all() and (a[:, 0] == np.arange(512)).all()
+        return True
+
+    assert all(run_ranks(3, body))
+
+
 # -- topology ------------------------------------------------------------------------------------------
 def test_topology_matches_the_reference_layout():
     """W=12, n_instances=3 (reference ddl/ddl_env.py:42-44,75-77)."""
