@@ -154,6 +154,9 @@ class Request:
             r.Wait()
 
 
+_ALL_COMMS = []
+
+
 class Intracomm:
     _ids = 0
 
@@ -165,6 +168,9 @@ class Intracomm:
         self.name = cid
         self._seq = {}
         self._coll = 0
+        self._segments = {}
+        self._attached = {}
+        _ALL_COMMS.append(self)
 
     # -- bookkeeping ------------------------------------------------------------------------------
     def Get_rank(self):
@@ -245,38 +251,44 @@ class Intracomm:
         return Request("recv", key, key + "/ack")
 
     def Sendrecv_replace(self, buf, dest, sendtag=0, source=0, recvtag=0):
-        """Bulk payloads travel through a POSIX shared-memory segment (all ranks share the node);
+        """Bulk payloads travel through POSIX shared-memory segments (all ranks share the node),
+        one persistent segment per (destination, tag) like a shared-memory BTL's eager buffers;
         only the segment's name goes through the store."""
         arr = np.asarray(buf)
         flat = arr.reshape(-1).view(np.uint8)
         seq = self._next("bs", dest, sendtag)
         key_s = f"{self.cid}/b/{self.rank}>{dest}/{sendtag}/{seq}"
-        seg = None
         if flat.size:
-            name = f"bddlmpi_{os.environ.get('BDDL_MPI_SESSION', 'x')}_sr_{abs(hash(key_s)) % (1 << 60):x}"
-            seg = shared_memory.SharedMemory(name=name, create=True, size=flat.size)
+            seg = self._segments.get((dest, sendtag))
+            if seg is None or seg.size < flat.size:
+                if seg is not None:
+                    seg.close()
+                    seg.unlink()
+                name = (f"bddlmpi_{os.environ.get('BDDL_MPI_SESSION', 'x')}_sr_{self.cid.replace('/', '_')}"
+                        f"_{self.rank}_{dest}_{sendtag}_{seq}")
+                seg = shared_memory.SharedMemory(name=name, create=True, size=flat.size)
+                self._segments[(dest, sendtag)] = seg
             np.frombuffer(seg.buf, dtype=np.uint8, count=flat.size)[:] = flat
-            _set(key_s, name.encode())
+            _set(key_s, seg.name.encode())
         else:
             _set(key_s, b"")
         seq = self._next("br", source, recvtag)
         key_r = f"{self.cid}/b/{source}>{self.rank}/{recvtag}/{seq}"
         name = _get(key_r).decode()
         if name:
-            src = shared_memory.SharedMemory(name=name)
-            try:
-                resource_tracker.unregister(src._name, "shared_memory")
-            except Exception:
-                pass
+            src = self._attached.get(name)
+            if src is None:
+                src = shared_memory.SharedMemory(name=name)
+                try:
+                    resource_tracker.unregister(src._name, "shared_memory")
+                except Exception:
+                    pass
+                self._attached[name] = src
             flat[:] = np.frombuffer(src.buf, dtype=np.uint8, count=flat.size)
-            src.close()
         _del(key_r)
         _set(key_r + "/ack", b"1")
-        _get(key_s + "/ack")  # the receiver has copied my payload
+        _get(key_s + "/ack")  # the receiver has copied my payload: the segment may be reused
         _del(key_s + "/ack")
-        if seg is not None:
-            seg.close()
-            seg.unlink()
 
     # -- collectives --------------------------------------------------------------------------------------
     def Ibarrier(self):
@@ -377,12 +389,19 @@ COMM_SELF = Intracomm([_RANK], f"self{_RANK}")
 
 
 def _finalize():
-    # keep the store's server (rank 0) alive until every rank is done
+    # keep the store's server (rank 0) alive until every rank is done, then drop bulk segments
     try:
         if _store is not None:
             COMM_WORLD.Barrier()
     except Exception:
         pass
+    for c in _ALL_COMMS:
+        for seg in c._segments.values():
+            try:
+                seg.close()
+                seg.unlink()
+            except Exception:
+                pass
 
 
 atexit.register(_finalize)
