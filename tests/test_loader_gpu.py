@@ -166,6 +166,21 @@ def test_process_transport_consumer_on_gpu(tmp_path):
     assert np.array_equal(np.load(os.path.join(str(tmp_path), "seen_0.npy")), exp)
 
 
+@pytest.mark.parametrize("host_pull", ["0", "1"])
+def test_process_transport_converts_on_the_gpu(tmp_path, host_pull):
+    """Producer process + GPU consumer with a fused cast: the borrowed host window is staged
+    (cudaMemcpyAsync) or pulled (zero-copy) and converted by the kernel."""
+    cfg = {"n_instances": 1, "n": 200, "v": 16, "B": 50, "epochs": 4, "fraction": 0.0, "cpu": False,
+           "convert": True, "small_ids": True}
+    os.environ["DDL_B200_HOST_PULL"] = host_pull
+    try:
+        _torchrun(2, cfg, tmp_path)
+    finally:
+        os.environ.pop("DDL_B200_HOST_PULL", None)
+    exp = expected_epochs(1, 1, 200, 50, 4, 0.0)[0] - 1_000_000  # producer 1 has rank_global 1
+    assert np.array_equal(np.load(os.path.join(str(tmp_path), "seen_0.npy")), exp)
+
+
 @pytest.mark.multigpu
 def test_two_gpus_push_exchange(tmp_path):
     """Push form: every GPU stores the samples it owns into its peer's batch ring over NVLink."""

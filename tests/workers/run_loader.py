@@ -23,12 +23,13 @@ class IdProducer(ddl.ProducerFunctionSkeleton):
     def on_init(self, **kw):
         super().on_init(**kw)
         self.rng = np.random.default_rng(seed=self.rank_global)
-        return ddl.DataProducerOnInitReturn(self.n, self.v, (self.n, self.v), (1, self.v - 1),
+        cv = ddl.Convert.cast_f32_bf16() if CFG.get("convert") else None
+        return ddl.DataProducerOnInitReturn(self.n, self.v, (self.n, self.v), (1, self.v - 1), convert=cv,
                                             shuffle_seed=self.rank_global if self.declare_seed else None)
 
     def post_init(self, **kw):
         self.my_ary = kw["my_ary"]
-        gid = self.rank_global * 1_000_000 + np.arange(self.n)
+        gid = (0 if CFG.get("small_ids") else self.rank_global * 1_000_000) + np.arange(self.n)
         self.my_ary[:, 0] = gid.astype(np.float32)
         self.my_ary[:, 1:] = (gid[:, None] % 97).astype(np.float32)
 
@@ -63,8 +64,8 @@ def body(env, conn):
         ids = []
         for i, (a, b) in enumerate(loader):
             assert a.shape == (B, 1) and b.shape == (B, v - 1)
-            ids.append(a.detach().cpu().numpy()[:, 0].astype(np.int64))
-            assert np.array_equal(b.cpu().numpy()[:, 0].astype(np.int64), ids[-1] % 97)
+            ids.append(a.detach().cpu().float().numpy()[:, 0].astype(np.int64))
+            assert np.array_equal(b.cpu().float().numpy()[:, 0].astype(np.int64), ids[-1] % 97)
             loader.mark(ddl.Marker.END_OF_BATCH)
         loader.mark(ddl.Marker.END_OF_EPOCH)
         seen.append(np.concatenate(ids))
