@@ -175,8 +175,6 @@ def run_ours(args) -> dict:
 
     def body(env, conn):
         B, rows = args.batch, args.rows
-        total = args.steps + args.warmup + 2
-        epochs = (total + rows // B - 1) // (rows // B) + 1
         loader = ddl.DistributedDataLoader(make_producer(rows), B, conn, 10**9, args.fraction, "sendrecv_replace",
                                            env.color, env.n_instances)
         ms, launches, clocks = timed_loop(loader, env, args.steps, args.warmup, e2e=False)

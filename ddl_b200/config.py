@@ -54,7 +54,6 @@ class LoaderConfig:
     # second time by the independent LDG form of the kernel and the two fingerprints are compared
     verify: bool = False
     trace: bool = False            # CUDA-event timing of every loader stage
-    fence_every_batch: bool = False
 
     @staticmethod
     def from_env(**overrides: Any) -> "LoaderConfig":
