@@ -221,6 +221,12 @@ def run_ours(args) -> dict:
         return {}
     ms_per_step = result["ms"] / args.steps
     value = args.gpus * args.batch / (ms_per_step * 1e-3)
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            hbm_peak, how = float(json.load(fh)["hbm_gbs"]), "measured"
+    except Exception:
+        hbm_peak, how = 6650.0, "fallback"
+    hbm_gbs = args.batch * SAMPLE * 3 / (ms_per_step * 1e6)  # uint8 read + bf16 write per GPU
     return {
         "metric": "gpu_delivered_samples_per_s", "value": round(value, 1), "unit": "samples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 5), "higher_is_better": True,
@@ -234,6 +240,9 @@ def run_ours(args) -> dict:
                      "nvlink_in_gbs_per_gpu": round(result.get("remote", 0.0) * args.batch * SAMPLE / (ms_per_step * 1e6), 1),
                      "frac_of_900_nominal": round(result.get("remote", 0.0) * args.batch * SAMPLE / (ms_per_step * 1e6) / 900, 3),
                      "frac_of_770_measured": round(result.get("remote", 0.0) * args.batch * SAMPLE / (ms_per_step * 1e6) / 770, 3)},
+        "roofline": {"hbm_gbs_per_gpu": round(hbm_gbs, 1), "hbm_peak_gbs": hbm_peak, "peak": how,
+                     "frac_of_hbm_copy": round(hbm_gbs / hbm_peak, 3),
+                     "bound": "HBM" if args.gpus == 1 else "NVLink (see exchange)"},
         "clocks": result["clocks"], "e2e": e2e, "gpu_launches": int(result["launches"]),
         "numerics_ok": result["ok"], "impl": "ddl_b200",
     }
