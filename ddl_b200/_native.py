@@ -193,3 +193,32 @@ def check(code: int) -> None:
 
 def launch_count() -> int:
     return int(lib().bddl_launch_count())
+
+
+# POSIX shared-memory names created by this process and not yet unlinked: removed at exit so that a
+# crash between create and unlink does not leave segments behind in /dev/shm.
+_shm_live: set = set()
+
+
+def shm_created(name: str) -> None:
+    _shm_live.add(name)
+
+
+def shm_unlinked(name: str) -> None:
+    _shm_live.discard(name)
+
+
+def _unlink_leftovers() -> None:
+    if _lib is None:
+        return
+    for name in list(_shm_live):
+        try:
+            _lib.bddl_shm_unlink(name.encode())
+        except Exception:
+            pass
+    _shm_live.clear()
+
+
+import atexit as _atexit  # noqa: E402
+
+_atexit.register(_unlink_leftovers)

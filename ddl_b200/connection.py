@@ -75,6 +75,7 @@ class Connection:
         if self.rank == 0:
             name = f"/bddl_flags_{uuid.uuid4().hex[:12]}"
             N.check(lib.bddl_shm_create(name.encode(), _FLAG_BYTES, C.byref(p)))
+            N.shm_created(name)
             C.memset(p.value, 0, _FLAG_BYTES)
             self.comm_per_gpu_shm.bcast_obj(name, 0)
         else:
@@ -84,6 +85,7 @@ class Connection:
         self.comm_per_gpu_shm.barrier()
         if self.rank == 0:
             lib.bddl_shm_unlink(name.encode())
+            N.shm_unlinked(name)
 
     def _flag(self, producer: int, which: int) -> C.c_void_p:
         return _word(self._flag_base, 16 + producer * _PER_PRODUCER + which)
@@ -163,12 +165,14 @@ class Connection:
             p = C.c_void_p()
             if target == self.rank:
                 N.check(lib.bddl_shm_create(name.encode(), nbytes, C.byref(p)))
+                N.shm_created(name)
             comm.barrier()
             if target != self.rank:
                 N.check(lib.bddl_shm_attach(name.encode(), nbytes, C.byref(p)))
             comm.barrier()
             if target == self.rank:
                 lib.bddl_shm_unlink(name.encode())
+                N.shm_unlinked(name)
             raw = np.ctypeslib.as_array((C.c_uint8 * nbytes).from_address(p.value))
             ary = raw[: math.prod(shape) * dt.itemsize].view(dt).reshape(shape)
             wins.append((p.value, nbytes))

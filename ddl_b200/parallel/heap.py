@@ -100,6 +100,7 @@ class SymmetricHeap:
         else:
             shm = f"/bddl_{self._session}_{self.comm.world_rank}_{len(self.local)}"
             N.check(lib.bddl_shm_create(shm.encode(), nbytes, C.byref(p)))
+            N.shm_created(shm)
             buf = Buffer(name, p.value, nbytes, self.device, shm_name=shm)
         self.local[name] = buf
         return buf
@@ -122,6 +123,7 @@ class SymmetricHeap:
         p = C.c_void_p()
         shm = f"/bddl_{self._session}_{self.comm.world_rank}_h{len(self.local)}"
         N.check(lib.bddl_shm_create(shm.encode(), nbytes, C.byref(p)))
+        N.shm_created(shm)
         buf = Buffer(name, p.value, nbytes, torch.device("cpu"), shm_name=shm)
         buf.host_shared = True
         buf.dev_ptr = 0
@@ -196,6 +198,7 @@ class SymmetricHeap:
             if self.device.type == "cpu" or getattr(b, "host_shared", False):
                 if b.shm_name:
                     lib.bddl_shm_unlink(b.shm_name.encode())
+                    N.shm_unlinked(b.shm_name)
                     b.shm_name = ""
 
     def peer_ptr(self, rank: int, name: str) -> int:
