@@ -113,3 +113,31 @@ extern "C" int bddl_host_gather_slots(void* h_dst, int64_t dst_row_bytes, const 
     g_pool->run(job);
     return 0;
 }
+
+// Out-of-place row permutation for declared shuffles of host windows: dst[i] = X[perm[i]] where X is
+// `src` with its first `ne` rows replaced by `recv_block` (the rows received in the global exchange;
+// null = no exchange).  Threaded: one pass over the window instead of numpy's three row copies per
+// Fisher-Yates step (reference tests/run_ddl.py:163-167).
+extern "C" int bddl_host_permute_rows(void* dst, const void* src, const void* recv_block, int64_t ne,
+                                      const int64_t* perm, int64_t n, int64_t row_bytes, int32_t n_threads) {
+    if (!dst || !src || (!perm && n > 0) || n < 0 || row_bytes <= 0 || ne < 0 || ne > n || dst == src)
+        return bddl_fail(BDDL_ERR_INVALID, "host_permute_rows: bad arguments");
+    for (int64_t i = 0; i < n; ++i)
+        if (perm[i] < 0 || perm[i] >= n) return bddl_fail(BDDL_ERR_INVALID, "host_permute_rows: perm[%lld] out of range", (long long)i);
+    if (n_threads < 1) n_threads = 1;
+    if (n_threads > 64) n_threads = 64;
+    std::vector<std::thread> th;
+    for (int t = 0; t < n_threads; ++t) {
+        th.emplace_back([=] {
+            const int64_t i0 = n * t / n_threads, i1 = n * (t + 1) / n_threads;
+            for (int64_t i = i0; i < i1; ++i) {
+                const int64_t j = perm[i];
+                const char* from = (recv_block && j < ne) ? (const char*)recv_block + j * row_bytes
+                                                          : (const char*)src + j * row_bytes;
+                memcpy((char*)dst + i * row_bytes, from, (size_t)row_bytes);
+            }
+        });
+    }
+    for (auto& x : th) x.join();
+    return 0;
+}

@@ -148,6 +148,7 @@ def _declare(lib: C.CDLL) -> None:
         "bddl_multicast_put": (C.c_int, [vp, vp, i64, vp]),
         "bddl_stage_slots_mt": (C.c_int, [vp, i64, vp, i32, i64, vp, i64, i64, vp, i32]),
         "bddl_host_gather_slots": (C.c_int, [vp, i64, vp, i32, i64, vp, i64, i64, i32]),
+        "bddl_host_permute_rows": (C.c_int, [vp, vp, vp, i64, vp, i64, i64, i32]),
         "bddl_stream_wait_value32": (C.c_int, [vp, vp, u32]),
         "bddl_stream_write_value32": (C.c_int, [vp, vp, u32]),
         "bddl_flag_signal": (C.c_int, [vp, i32, u32, i32, vp]),

@@ -135,9 +135,14 @@ class Connection:
         return [self.comm_per_gpu_shm.recv(source=t, tag=0) for t in range(1, self.comm_per_gpu_shm.Get_size())]
 
     # -- windows (reference ddl/connection.py:88-139) ---------------------------------------------------
-    def init_windows(self, shapes, dtypes=None) -> List[Optional[np.ndarray]]:
+    def init_windows(self, shapes, dtypes=None, double=False) -> List[Optional[np.ndarray]]:
         """Process transport: one shared-memory array per producer, mapped by every rank of the
-        instance.  ``shapes`` is one shape (producer side) or one per producer (consumer side)."""
+        instance.  ``shapes`` is one shape (producer side) or one per producer (consumer side).
+
+        ``double`` (producer side: this producer's choice) allocates a second window per producer --
+        the scheme the reference sketches but never built (reference ddl/mpi_dataloader.py:19-28):
+        the producer fills one window while the consumer reads the other.  Which one is current
+        follows from the hand-over count (``current_window``)."""
         if self.transport == "device":
             raise RuntimeError("device transport keeps windows as slot tables; see DeviceEngine")
         comm = self.comm_per_gpu_shm
@@ -150,18 +155,21 @@ class Connection:
             dtypes = [dtypes] * (size - 1)
         # every rank learns every producer's geometry (Shared_query in the reference)
         mine = None if self.rank == 0 else (tuple(int(x) for x in shapes[self.rank - 1]),
-                                            np.dtype(dtypes[self.rank - 1]).str)
+                                            np.dtype(dtypes[self.rank - 1]).str, bool(double))
         info = comm.allgather_obj(mine)
         shapes = [info[t][0] for t in range(1, size)]
         dtypes = [np.dtype(info[t][1]) for t in range(1, size)]
+        doubles = [info[t][2] for t in range(1, size)]
         lib = N.lib()
         wins, arys = [], []
+        self.wins_alt, self.arys_alt = [None] * (size - 1), [None] * (size - 1)
         session = comm.bcast_obj(uuid.uuid4().hex[:10] if self.rank == 0 else None, 0)
-        for target in range(1, size):
+        jobs = [(t, 0) for t in range(1, size)] + [(t, 1) for t in range(1, size) if doubles[t - 1]]
+        for target, which in jobs:
             shape = tuple(int(x) for x in shapes[target - 1])
             dt = np.dtype(dtypes[target - 1])
             nbytes = max(16, math.prod(shape) * dt.itemsize)
-            name = f"/bddl_win_{session}_{target}"
+            name = f"/bddl_win_{session}_{target}_{which}"
             p = C.c_void_p()
             if target == self.rank:
                 N.check(lib.bddl_shm_create(name.encode(), nbytes, C.byref(p)))
@@ -175,10 +183,21 @@ class Connection:
                 N.shm_unlinked(name)
             raw = np.ctypeslib.as_array((C.c_uint8 * nbytes).from_address(p.value))
             ary = raw[: math.prod(shape) * dt.itemsize].view(dt).reshape(shape)
-            wins.append((p.value, nbytes))
-            arys.append(ary)
+            if which == 0:
+                wins.append((p.value, nbytes))
+                arys.append(ary)
+            else:
+                self.wins_alt[target - 1] = (p.value, nbytes)
+                self.arys_alt[target - 1] = ary
         self.wins = wins
         return arys
+
+    def current_window(self, target_rank: int) -> int:
+        """0 = primary, 1 = second window of producer ``target_rank`` for the hand-over in progress:
+        iteration t (0-based) of a double-window producer lands in window (t + 1) & 1."""
+        if not getattr(self, "arys_alt", None) or self.arys_alt[target_rank - 1] is None:
+            return 0
+        return (self._counts[target_rank] + 1) & 1
 
     def lock_windows(self) -> None:
         """MPI passive-target epochs have no counterpart: ordering comes from the flags."""
@@ -197,9 +216,9 @@ class Connection:
         lib = N.lib()
         for i in range(len(arys)):
             arys[i] = None
-        for p, n in self.wins:
+        for p, n in list(self.wins) + [w for w in getattr(self, "wins_alt", []) if w is not None]:
             lib.bddl_shm_detach(C.c_void_p(p), n)
-        self.wins = []
+        self.wins, self.wins_alt, self.arys_alt = [], [], []
         if self._flag_base:
             lib.bddl_shm_detach(C.c_void_p(self._flag_base), _FLAG_BYTES)
             self._flag_base = 0

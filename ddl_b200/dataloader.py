@@ -182,11 +182,16 @@ class DistributedDataLoader(DistributedDataloaderABC):
                               for _ in range(self.cfg.fetch_streams)]
         self.fetch = self.fetch_streams[0]
         lib = N.lib()
-        self._win_dev = []
-        for (ptr, nbytes) in conn.wins:  # pin + map every borrowed window once
-            d = C.c_void_p()
-            N.check(lib.bddl_host_register(C.c_void_p(ptr), nbytes, C.byref(d)))
-            self._win_dev.append(int(d.value))
+        self._win_dev, self._win_dev_alt, self._registered = [], [], []
+        for primary, alt in zip(conn.wins, conn.wins_alt):  # pin + map every borrowed window once
+            for win, out in ((primary, self._win_dev), (alt, self._win_dev_alt)):
+                if win is None:
+                    out.append(0)
+                    continue
+                d = C.c_void_p()
+                N.check(lib.bddl_host_register(C.c_void_p(win[0]), win[1], C.byref(d)))
+                self._registered.append(win[0])
+                out.append(int(d.value))
         B = self.batch_size
         stage_row = max(s.sample_bytes for s in self.specs)
         out_row = max(s.dst_row_bytes for s in self.specs)
@@ -201,8 +206,10 @@ class DistributedDataLoader(DistributedDataloaderABC):
             if not kernel_ok:
                 raise ValueError("converting windows need rows that are a multiple of 16 bytes")
             if self.cfg.host_pull:
-                table = SourceTable([self._win_dev[k]], self.device)
-                slots = torch.arange(s.nData, dtype=torch.int64, device=self.device)
+                # source 0 = primary window, source 1 = the producer's second window (if any)
+                table = SourceTable([self._win_dev[k], self._win_dev_alt[k] or self._win_dev[k]], self.device)
+                slots = torch.stack([torch.arange(s.nData, dtype=torch.int64) + make_slot(w, 0)
+                                     for w in (0, 1)]).to(self.device)
             else:
                 table = SourceTable([t.data_ptr() for t in self._stage], self.device)
                 slots = torch.stack([torch.arange(B, dtype=torch.int64) + make_slot(i, 0) for i in range(depth)]).to(self.device)
@@ -231,7 +238,8 @@ class DistributedDataLoader(DistributedDataloaderABC):
         if self.transport == "process" and not self.cuda:
             # zero-copy views of the shared window (reference ddl/mpi_dataloader.py:190-198)
             start = self.batch_size * b
-            data = torch.from_numpy(self.arys[k][start:start + self.batch_size])
+            win = self.connection.arys_alt[k] if self.connection.current_window(k + 1) else self.arys[k]
+            data = torch.from_numpy(win[start:start + self.batch_size])
             self.metrics.batch(self.batch_size, data.numel() * data.element_size(), 0)
             return torch.split(data, list(self.splits[k]), dim=1)
         hit = self._pref.pop((self._lend_seq, b), None)
@@ -299,11 +307,13 @@ class DistributedDataLoader(DistributedDataloaderABC):
             lib = N.lib()
             fs = C.c_void_p(stream.cuda_stream)
             plan = self._plans[k]
+            which = self.connection.current_window(k + 1)
             if self.cfg.host_pull:
                 p, slots = plan
-                p.run_ptr(slots.data_ptr() + b * B * 8, self._out[slot].data_ptr(), B, stream.cuda_stream)
+                p.run_ptr(slots[which].data_ptr() + b * B * 8, self._out[slot].data_ptr(), B, stream.cuda_stream)
             else:
-                src = self.connection.wins[k][0] + b * B * s.sample_bytes
+                base = self.connection.wins_alt[k][0] if which else self.connection.wins[k][0]
+                src = base + b * B * s.sample_bytes
                 N.check(lib.bddl_memcpy_async(C.c_void_p(self._stage[slot].data_ptr()), C.c_void_p(src),
                                               B * s.sample_bytes, 1, fs))
                 if plan is not None:
@@ -400,7 +410,7 @@ class DistributedDataLoader(DistributedDataloaderABC):
             return
         if self.cuda:
             torch.cuda.synchronize(self.device)
-            for (ptr, _n) in self.connection.wins:
+            for ptr in self._registered:
                 N.lib().bddl_host_unregister(C.c_void_p(ptr))
             self._stage, self._out, self._plans = [], [], []
         self.connection.Barrier()

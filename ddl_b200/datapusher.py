@@ -87,9 +87,17 @@ class DataPusher(DataPusherABC):
         self.metadata_to_consumer = _meta_from_init(on_init_return, self.metadata_from_consumer.batch_size)
         connection.send_metadata(self.metadata_to_consumer, "producer")
 
+        # A declared shuffle (shuffle_seed) runs natively, out of place, between two windows: the
+        # producer prepares iteration t+1 while the consumer still reads iteration t.
+        cfg = connection.config
+        self.declared = (on_init_return.shuffle_seed is not None and cfg.shuffle_mode in ("auto", "device")
+                         and not getattr(on_init_return, "variable_length", False))
         self.arys = connection.init_windows(shapes=self.metadata_to_consumer.shape,
-                                            dtypes=self.metadata_to_consumer.dtype)
+                                            dtypes=self.metadata_to_consumer.dtype, double=self.declared)
         self.my_ary = self.arys[self.rank_per_gpu_shm - 1]  # rank 0 is the consumer and owns no window
+        self.windows = [self.my_ary, connection.arys_alt[self.rank_per_gpu_shm - 1]]
+        self.cur = 0
+        self.shuffle_rng = Pcg64(on_init_return.shuffle_seed) if self.declared else None
         connection.lock_windows()
 
         num_exchange = int(on_init_return.nData * self.metadata_from_consumer.global_shuffle_fraction_exchange)
@@ -120,9 +128,53 @@ class DataPusher(DataPusherABC):
         self.connection.unlock_windows()
         self.connection.finalize(self.arys)
 
+    def _prepare_declared(self) -> None:
+        """One producer iteration in declared mode: (exchange +) shuffle from the current window
+        into the other one, natively and threaded; same rows in the same order as
+        global_shuffle() followed by rng.shuffle(my_ary) (reference ddl/datapusher.py:152-154)."""
+        import ctypes as C
+
+        from . import _native as N
+
+        src, dst = self.windows[self.cur], self.windows[self.cur ^ 1]
+        n = src.shape[0]
+        recv, ne = None, 0
+        gs = self.global_shuffler
+        if gs is not None and not self.compat:
+            send_to, recv_from = gs._calculate_comm_partner()
+            ne, half = gs.num_exchange, gs.num_exchange // 2
+            recv = np.ascontiguousarray(src[:ne]).copy()
+            gs.comm_nth_pusher.sendrecv_replace(recv[:half], dest=send_to, source=recv_from, sendtag=50, recvtag=50)
+            gs.comm_nth_pusher.sendrecv_replace(recv[half:ne], dest=recv_from, source=send_to, sendtag=51, recvtag=51)
+        perm = self.shuffle_rng.permutation(n)
+        N.check(N.lib().bddl_host_permute_rows(
+            dst.ctypes.data, src.ctypes.data, recv.ctypes.data if recv is not None else None, ne,
+            perm.ctypes.data, n, src.strides[0], self.connection.config.host_threads))
+        self.cur ^= 1
+        self.iterations += 1
+        self.connection.heartbeat(self.rank_per_gpu_shm)
+
+    def _push_declared(self) -> None:
+        cbs, compat = self.callbacks, self.compat
+        self._prepare_declared()
+        while True:
+            if self._iend_access_epoch() is WorkerInfo.STOP:
+                break
+            # the consumer reads windows[cur]; it returned the other window before borrowing this
+            # one, so the next iteration can be prepared right now
+            self._prepare_declared()
+            if self._istart_access_epoch() is WorkerInfo.STOP:
+                break
+            execute_callbacks("on_shuffle_end", callbacks=cbs, compat=compat)
+
     def push_data(self) -> None:
         cbs, compat = self.callbacks, self.compat
         execute_callbacks("on_push_begin", callbacks=cbs, compat=compat)
+        if self.declared:
+            self._push_declared()
+            execute_callbacks("on_push_end", callbacks=cbs, compat=compat)
+            self._finalize()
+            return
         while True:
             execute_callbacks("global_shuffle", callbacks=cbs, compat=compat)
             self.sync()

@@ -202,6 +202,13 @@ int bddl_host_gather_slots(void* h_dst, int64_t dst_row_bytes, const void* const
                            int64_t row_bytes, const uint64_t* slots, int64_t n, int64_t copy_bytes,
                            int32_t n_threads);
 
+/* Declared shuffle of a host window, out of place and threaded: dst[i] = X[perm[i]], X = src with
+ * its first ne rows replaced by recv_block (rows received in the global exchange, or NULL).
+ * Replaces rng.shuffle(my_ary) (tests/run_ddl.py:163-167) + the in-place Sendrecv_replace
+ * (ddl/shuffle.py:95-108) for producer processes with two windows. */
+int bddl_host_permute_rows(void* dst, const void* src, const void* recv_block, int64_t ne, const int64_t* perm,
+                           int64_t n, int64_t row_bytes, int32_t n_threads);
+
 /* ---- N8: flags (replace the zero-byte token messages, Win.Sync and the Ibarrier shutdown,
  *      ddl/connection.py:61-63,153-187).  Device side: counters in the symmetric heap. ------- */
 int bddl_stream_wait_value32(void* stream, uint32_t* d_addr, uint32_t value);   /* wait *addr >= value */

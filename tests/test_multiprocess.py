@@ -105,3 +105,15 @@ def test_dedicated_storage_ranks_one_to_three(tmp_path):
            "fraction": 0.5, "shuffle_mode": "device", "declare_seed": True}
     run_world(4, cfg, tmp_path)
     check(tmp_path, 3, 2, cfg)
+
+
+@pytest.mark.timeout(200)
+def test_process_transport_declared_shuffle_double_windows(tmp_path):
+    """Producer processes with a declared shuffle: two windows each, native out-of-place shuffle
+    (+ out-of-place exchange) one iteration ahead -- same order as the reference semantics."""
+    cfg = {"n_instances": 2, "n": 2000, "v": 4, "B": 256, "epochs": 5, "fraction": 0.5, "declare_seed": True}
+    run_world(4, cfg, tmp_path)
+    check(tmp_path, 2, 1, cfg)
+    cfg = {"n_instances": 1, "n": 3000, "v": 9, "B": 512, "epochs": 7, "fraction": 0.5, "declare_seed": True}
+    run_world(3, cfg, tmp_path)
+    check(tmp_path, 1, 2, cfg)
