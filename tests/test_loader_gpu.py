@@ -158,9 +158,12 @@ def _torchrun(nproc, cfg, tmp_path, timeout=240):
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
 
 
-def test_process_transport_consumer_on_gpu(tmp_path):
-    """Reference layout on one GPU: the consumer stages the borrowed host window to the device."""
-    cfg = {"n_instances": 1, "n": 4000, "v": 8, "B": 256, "epochs": 4, "fraction": 0.5, "cpu": False}
+@pytest.mark.parametrize("declare", [False, True])
+def test_process_transport_consumer_on_gpu(tmp_path, declare):
+    """Reference layout on one GPU: the consumer stages the borrowed host window to the device
+    (with a declared shuffle: from whichever of the producer's two windows is current)."""
+    cfg = {"n_instances": 1, "n": 4000, "v": 8, "B": 256, "epochs": 4, "fraction": 0.5, "cpu": False,
+           "declare_seed": declare}
     _torchrun(3, cfg, tmp_path)
     exp = expected_epochs(1, 2, 4000, 256, 4, 0.5)[0]
     assert np.array_equal(np.load(os.path.join(str(tmp_path), "seen_0.npy")), exp)
