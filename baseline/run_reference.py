@@ -54,6 +54,16 @@ def run_reference(args) -> dict:
     if rank != 0:
         return {}  # the reference world is started by rank 0 alone; the other launcher ranks idle
     if not os.path.isdir(os.path.join(HERE, "_ref", "ddl")):
+        try:  # the install is git-ignored; redo it when the reference source is at hand
+            import contextlib
+
+            import install_reference
+
+            with contextlib.redirect_stdout(sys.stderr):
+                install_reference.main()
+        except Exception:
+            pass
+    if not os.path.isdir(os.path.join(HERE, "_ref", "ddl")):
         return {"impl": "reference", "unavailable": "baseline/_ref/ddl missing: run python baseline/install_reference.py"}
     n = args.gpus
     cores = os.cpu_count() or 8
