@@ -13,8 +13,10 @@ Modes (BDDL_REF_CFG json):
 harness's producer function -- which is callbacks[0] -- defines global_shuffle() itself and forwards
 to the reference's own SendRecvReplaceGlobalShuffler.  No reference file is edited either way.
 """
+import faulthandler
 import json
 import os
+import sys
 import time
 
 import numpy as np
@@ -104,46 +106,70 @@ def main(cfg, mpi_env, conn):
         np.save(os.path.join(cfg["out"], f"ref_seen_{inst}.npy"), np.stack(seen))
         return
 
-    # bench: deliver normalised bf16 batches to this consumer's GPU
+    # bench: deliver normalised bf16 batches to this consumer's GPU.  One run measures both numbers:
+    # phase 1 = `timed` steps device-timed (CUDA events, no per-step synchronisation), phase 2 = the
+    # same number of steps end to end (per step: pageable H2D of the batch, normalise, a 4-byte D2H
+    # read of a result and a stream synchronise; wall clock).
     use_cuda = torch.cuda.is_available() and not cfg.get("cpu")
     dev = torch.device("cuda", inst % torch.cuda.device_count()) if use_cuda else torch.device("cpu")
+    if use_cuda:
+        torch.cuda.set_device(dev)  # pinned allocations and events belong to this consumer's GPU
     hw = v * 4 // 3
     scale = torch.tensor([1.0 / (255.0 * s) for s in STD], device=dev).view(1, 3, 1)
     bias = torch.tensor([-m / s for m, s in zip(MEAN, STD)], device=dev).view(1, 3, 1)
-    steps, warm, e2e = cfg["steps"], cfg["warmup"], cfg.get("e2e", False)
-    done, t0, ev0, ev1, checks = 0, None, None, None, 0.0
+    timed, warm = cfg["steps"], cfg["warmup"]
     host_out = torch.empty(1).pin_memory() if use_cuda else torch.empty(1)
-    finished = False
+    res_path = os.path.join(cfg["out"], f"ref_bench_{inst}.json")
+    res = {"steps": timed, "device": str(dev)}
+    done, checks = 0, 0.0
+    ev0 = ev1 = t0 = None
+
+    def sync():
+        if use_cuda:
+            torch.cuda.synchronize(dev)
+
+    def save():
+        with open(res_path + ".tmp", "w") as fh:
+            json.dump(res, fh)
+        os.replace(res_path + ".tmp", res_path)
+
     for _ in range(E):
         for i, (x,) in enumerate(loader):
-            if not finished:
-                if done == warm:
+            phase = 0 if done < warm else (1 if done < warm + timed else (2 if done < warm + 2 * timed else 3))
+            if phase < 3:
+                if done == warm:  # phase 1 starts
+                    sync()
                     if use_cuda:
-                        torch.cuda.synchronize(dev)
                         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                         ev0.record()
+                    t0 = time.perf_counter()
+                elif done == warm + timed:  # phase 1 ends, phase 2 starts
+                    if use_cuda:
+                        ev1.record()
+                    sync()
+                    res["ms_device"] = ev0.elapsed_time(ev1) if use_cuda else (time.perf_counter() - t0) * 1e3
+                    save()
                     t0 = time.perf_counter()
                 u8 = x.view(torch.uint8)                       # [B, 3*H*W] bytes of the shared window
                 d = u8.to(dev)                                 # pageable host -> device
                 y = (d.view(B, 3, hw).float() * scale + bias).to(torch.bfloat16)
-                if e2e:
+                if phase == 2:
                     host_out.copy_(y[0, 0, :64].float().sum().reshape(1), non_blocking=True)
                     if use_cuda:
                         torch.cuda.current_stream(dev).synchronize()
                     checks += float(host_out[0])
                 done += 1
-                if done == warm + steps:
-                    if use_cuda:
-                        ev1.record()
-                        torch.cuda.synchronize(dev)
-                    wall = time.perf_counter() - t0
-                    ms_dev = ev0.elapsed_time(ev1) if use_cuda else wall * 1e3
-                    with open(os.path.join(cfg["out"], f"ref_bench_{inst}.json"), "w") as fh:
-                        json.dump({"ms_device": ms_dev, "ms_wall": wall * 1e3, "steps": steps, "device": str(dev)}, fh)
-                    finished = True
+                if done == warm + 2 * timed:
+                    sync()
+                    res["ms_e2e"] = (time.perf_counter() - t0) * 1e3
+                    res["check"] = checks
+                    save()
             loader.mark(ddl.Marker.END_OF_BATCH)
         loader.mark(ddl.Marker.END_OF_EPOCH)
 
 
 if __name__ == "__main__":
+    # a rank still running after `watchdog` seconds dumps every thread's stack into its stderr log,
+    # so a hang names its own line (the harness surfaces the log tail in the bench JSON)
+    faulthandler.dump_traceback_later(float(CFG.get("watchdog", 240)), exit=False, file=sys.stderr)
     main(CFG)

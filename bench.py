@@ -6,7 +6,12 @@ in HBM.  One process per GPU (torchrun), weak scaling (fixed shard and batch per
 
   value   device-timed (CUDA events, max over ranks) samples/s over all GPUs with the shards
           resident in HBM -- the product's main path: one exchange_gather_collate launch per
-          batch pulls rows from every peer over NVLink, converts and collates them.
+          batch pulls rows from every peer over NVLink, converts and collates them.  The timed
+          region repeats the requested --steps until it lasts >= --min-seconds and spans several
+          window turnovers (the per-epoch index_exchange + perm_gen + barrier are inside it); its
+          end event waits for every fetch stream; one batch per rank is compared bit for bit with
+          an independent fetch + fp32 PyTorch expression; a value that breaks a physical limit
+          (NVLink 900 GB/s, HBM 7.7 TB/s) is not printed.
   e2e     the same metric through the same public API with the dataset resident in pinned
           host memory: every step copies that step's raw samples host->device and reads a
           checksum of the delivered batch back to the host.
@@ -19,10 +24,7 @@ from __future__ import annotations
 import argparse
 import json
 import os
-import subprocess
 import sys
-import threading
-import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -30,49 +32,6 @@ sys.path.insert(0, ROOT)
 MEAN, STD = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
 C_, H_, W_ = 3, 224, 224
 SAMPLE = C_ * H_ * W_
-
-
-class ClockSampler:
-    """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md recipe)."""
-
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
-
-    def __init__(self, device_index: int):
-        self.idx, self.rows, self.proc = device_index, [], None
-
-    def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
-        except Exception:
-            self.proc = None
-
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
-
-    def stop(self) -> dict:
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[1]))
-                mx.append(float(r[2]))
-                for n, v in zip(names, r[4:8]):
-                    if v.lower().startswith("active"):
-                        reasons.add(n)
-            except Exception:
-                pass
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
 
 
 def make_producer(rows: int, seed_base: int = 1234):
@@ -108,83 +67,24 @@ def make_producer(rows: int, seed_base: int = 1234):
 
 
 def run_ours(args) -> dict:
-    import numpy as np
-    import torch
-
     import ddl_b200 as ddl
-    from ddl_b200 import _native as N
+    from ddl_b200.utils.benchmarking import check_numerics, timed_loop
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
-    result = {}
-
-    def timed_loop(loader, env, steps, warmup, e2e: bool):
-        dev = env.device
-        main = torch.cuda.current_stream(dev)
-        host_out = torch.empty(1, dtype=torch.int64).pin_memory()
-        it = iter(_steps(loader))
-        for _ in range(warmup):
-            next(it)
-        torch.cuda.synchronize(dev)
-        env.comm_global.barrier()
-        torch.cuda.synchronize(dev)
-        l0 = N.launch_count()
-        launches = 0
-        sampler = ClockSampler(dev.index or 0)
-        if env.comm_global.rank == 0 and not e2e:
-            sampler.start()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0 = time.perf_counter()
-        a.record(main)
-        for _ in range(steps):
-            x = next(it)
-            if e2e:  # device->host read of the step's result: a checksum of the delivered batch
-                host_out.copy_(loader.batch_checksum(), non_blocking=True)
-                main.synchronize()
-        b.record(main)
-        torch.cuda.synchronize(dev)
-        wall = time.perf_counter() - t0
-        launches = N.launch_count() - l0
-        if not e2e:
-            # the timed region lasts milliseconds, shorter than one nvidia-smi sampling period:
-            # keep the identical loop running (untimed) so the clock record covers the same load
-            # (same step count on every rank: epoch boundaries are collective)
-            extra = env.comm_global.bcast_obj(int(min(200000, 0.8 / max(wall / steps, 1e-6))), 0)
-            for i in range(extra):
-                next(it)
-                if i % 256 == 255:
-                    torch.cuda.synchronize(dev)
-            torch.cuda.synchronize(dev)
-        env.comm_global.barrier()
-        clocks = sampler.stop() if (env.comm_global.rank == 0 and not e2e) else None
-        if clocks is not None:
-            clocks["note"] = "sampled every 100 ms while the timed loop and its untimed continuation ran"
-        ms = a.elapsed_time(b)
-        if e2e:
-            ms = max(ms, wall * 1e3)
-        all_ms = env.comm_global.allgather_obj(ms)
-        return max(all_ms), launches, clocks
-
-    def _steps(loader):
-        while True:
-            for (x,) in loader:
-                yield x
-                loader.mark(ddl.Marker.END_OF_BATCH)
-            loader.mark(ddl.Marker.END_OF_EPOCH)
+    result = {"rank": int(os.environ.get("RANK", "0"))}
 
     def body(env, conn):
         B, rows = args.batch, args.rows
         loader = ddl.DistributedDataLoader(make_producer(rows), B, conn, 10**9, args.fraction, "sendrecv_replace",
                                            env.color, env.n_instances)
-        ms, launches, clocks = timed_loop(loader, env, args.steps, args.warmup, e2e=False)
-        # numerics spot check of one delivered batch against the fp32 PyTorch statement
+        t = timed_loop(loader, env, args.steps, args.warmup, False, args.min_seconds, int(2.5 * (rows // B)),
+                       sample_clocks=env.comm_global.rank == 0)
         remote = max(env.comm_global.allgather_obj(loader.remote_fraction()))
-        (x,) = loader[0]
-        ok = bool(torch.isfinite(x.float()).all().item()) and x.shape == (B, SAMPLE) and x.dtype == torch.bfloat16
+        nums = env.comm_global.allgather_obj(check_numerics(loader, t.pop("it")))
         loader.close()
-        result.update(ms=ms, launches=launches, clocks=clocks, ok=ok, n=env.n_instances, rank=env.comm_global.rank,
-                      remote=remote)
+        result.update(main=t, remote=remote, numerics=nums, n=env.n_instances)
 
     cfg = ddl.LoaderConfig.from_env(metrics=False, ring_depth=args.ring, gather_variant=args.variant,
                                     gather_tune=args.tune, prefetch_depth=args.prefetch_depth,
@@ -192,8 +92,6 @@ def run_ours(args) -> dict:
                                     gather_max_ctas=args.max_ctas)
     if not args.e2e_only:
         ddl.distributed_dataloader(body, n_instances="world", n_producers=1, config=cfg)()
-    else:
-        result.update(ms=1.0, launches=0, clocks=None, ok=True, rank=int(os.environ.get("RANK", "0")), remote=0.0)
 
     e2e = None
     if not args.no_e2e:
@@ -201,25 +99,44 @@ def run_ours(args) -> dict:
             B, rows = args.batch, min(args.rows, args.e2e_rows)
             loader = ddl.DistributedDataLoader(make_producer(rows), B, conn, 10**9, args.fraction,
                                                "sendrecv_replace", env.color, env.n_instances)
-            steps = max(32, min(args.steps, 128))
-            ms, _, _ = timed_loop(loader, env, steps, max(args.warmup, rows // B + 2), e2e=True)
+            t = timed_loop(loader, env, args.steps, args.warmup, True, args.e2e_min_seconds, int(2.5 * (rows // B)),
+                           sample_clocks=False)
+            nums = env.comm_global.allgather_obj(check_numerics(loader, t.pop("it")))
             loader.close()
-            result.update(e2e_ms=ms, e2e_steps=steps)
+            result.update(e2e=t, e2e_numerics=nums)
 
         cfg2 = ddl.LoaderConfig.from_env(metrics=False, ring_depth=3, residency="host",
                                          host_stage=args.host_stage, host_threads=args.host_threads, gather_variant=args.e2e_variant,
                                          gather_tune=args.e2e_tune)
         ddl.distributed_dataloader(body_e2e, n_instances="world", n_producers=1, config=cfg2)()
-        v = args.gpus * args.batch * result["e2e_steps"] / (result["e2e_ms"] * 1e-3)
-        e2e = {"value": round(v, 1), "unit": "samples/s", "h2d_bytes_per_step": args.batch * SAMPLE,
-               "d2h_bytes_per_step": 8, "steps": result["e2e_steps"],
+        t = result["e2e"]
+        v = args.gpus * args.batch * t["total_steps"] / (t["ms"] * 1e-3)
+        bad = sum(n["mismatched_rows"] for n in result["e2e_numerics"])
+        e2e = {"value": round(v, 1) if bad == 0 else None, "unit": "samples/s", "h2d_bytes_per_step": args.batch * SAMPLE,
+               "d2h_bytes_per_step": 8, "steps": args.steps, "repeats": t["repeats"],
+               "ms_per_step": round(t["ms"] / t["total_steps"], 5), "timed_region_s": round(t["ms"] * 1e-3, 3),
+               "pcie_gbs_per_gpu": round(args.batch * SAMPLE * t["total_steps"] / (t["ms"] * 1e6), 2),
+               "numerics": {"mismatched_rows": bad, "rows_checked": sum(n["rows"] for n in result["e2e_numerics"])},
                "path": {"gather": "pinned host shard -> threaded CPU gather -> one cudaMemcpyAsync per step -> convert kernel -> batch checksum kernel -> 8-byte D2H",
                         "memcpy": "pinned host shard -> cudaMemcpyAsync per row -> convert kernel -> batch checksum kernel -> 8-byte D2H",
                         "pull": "pinned host shard -> kernel pulls rows over PCIe (zero-copy) + convert -> batch checksum kernel -> 8-byte D2H"}[args.host_stage]}
 
-    if result.get("rank", 0) != 0:
+    if result["rank"] != 0:
         return {}
-    ms_per_step = result["ms"] / args.steps
+    config = {"model": "imagenet_u8_3x224x224_loader", "global_batch": args.batch * args.gpus, "seq_len": SAMPLE,
+              "parallelism": f"dp{args.gpus}", "per_gpu_batch": args.batch, "fraction_exchange": args.fraction,
+              "l2": "inputs larger than L2 (every row is read once per epoch)"}
+    out = {"metric": "gpu_delivered_samples_per_s", "value": None, "unit": "samples/s", "n_gpus": args.gpus,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": config,
+           "impl": "ddl_b200", "e2e": e2e, "gpu_launches": 0,
+           "details": {"rows_per_gpu": args.rows, "exchange": args.exchange, "ring": args.ring,
+                       "prefetch_depth": args.prefetch_depth, "fetch_streams": args.fetch_streams}}
+    if args.e2e_only:
+        out["gpu_launches"] = int(result["e2e"]["launches"])
+        return out
+    t = result["main"]
+    ms_per_step = t["ms"] / t["total_steps"]
     value = args.gpus * args.batch / (ms_per_step * 1e-3)
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
@@ -227,25 +144,40 @@ def run_ours(args) -> dict:
     except Exception:
         hbm_peak, how = 6650.0, "fallback"
     hbm_gbs = args.batch * SAMPLE * 3 / (ms_per_step * 1e6)  # uint8 read + bf16 write per GPU
-    return {
-        "metric": "gpu_delivered_samples_per_s", "value": round(value, 1), "unit": "samples/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 5), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"model": "imagenet_u8_3x224x224_loader", "global_batch": args.batch * args.gpus,
-                   "seq_len": SAMPLE, "parallelism": f"dp{args.gpus}", "per_gpu_batch": args.batch,
-                   "rows_per_gpu": args.rows, "fraction_exchange": args.fraction, "exchange": args.exchange,
-                   "l2": "inputs larger than L2 (shard %.1f GB per GPU, every row read once per epoch)"
-                         % (args.rows * SAMPLE / 1e9)},
-        "exchange": {"remote_fraction": round(result.get("remote", 0.0), 4),
-                     "nvlink_in_gbs_per_gpu": round(result.get("remote", 0.0) * args.batch * SAMPLE / (ms_per_step * 1e6), 1),
-                     "frac_of_900_nominal": round(result.get("remote", 0.0) * args.batch * SAMPLE / (ms_per_step * 1e6) / 900, 3),
-                     "frac_of_770_measured": round(result.get("remote", 0.0) * args.batch * SAMPLE / (ms_per_step * 1e6) / 770, 3)},
+    nvl = result["remote"] * args.batch * SAMPLE / (ms_per_step * 1e6)
+    bad = sum(n["mismatched_rows"] for n in result["numerics"])
+    finite = all(n["finite"] for n in result["numerics"])
+    # a value that breaks physics or numerics is not printed
+    problems = []
+    if nvl > 900.0:
+        problems.append(f"NVLink inbound {nvl:.0f} GB/s per GPU exceeds the 900 GB/s link rate")
+    if hbm_gbs > 7700.0:
+        problems.append(f"HBM traffic {hbm_gbs:.0f} GB/s exceeds the 7700 GB/s nominal rate")
+    if bad or not finite:
+        problems.append(f"{bad} delivered rows differ from the fp32 PyTorch reference")
+    out.update({
+        "value": None if problems else round(value, 1), "ms_per_step": round(ms_per_step, 5),
+        "repeats": t["repeats"], "timed_steps_total": t["total_steps"], "timed_region_s": round(t["ms"] * 1e-3, 4),
+        "windows_crossed": t["windows_crossed"],
+        "timing": "CUDA events on the training stream, end event ordered after every fetch stream; "
+                  "the driver's --steps is repeated `repeats` times back to back and the mean is reported, so the "
+                  "region lasts >= %.2f s and spans >= 2 window turnovers (index_exchange + perm_gen + "
+                  "cross-rank barrier included)" % args.min_seconds,
+        "exchange": {"remote_fraction": round(result["remote"], 4), "nvlink_in_gbs_per_gpu": round(nvl, 1),
+                     "frac_of_900_nominal": round(nvl / 900, 3), "frac_of_770_measured": round(nvl / 770, 3)},
         "roofline": {"hbm_gbs_per_gpu": round(hbm_gbs, 1), "hbm_peak_gbs": hbm_peak, "peak": how,
                      "frac_of_hbm_copy": round(hbm_gbs / hbm_peak, 3),
                      "bound": "HBM" if args.gpus == 1 else "NVLink (see exchange)"},
-        "clocks": result["clocks"], "e2e": e2e, "gpu_launches": int(result["launches"]),
-        "numerics_ok": result["ok"], "impl": "ddl_b200",
-    }
+        "clocks": t["clocks"], "gpu_launches": int(t["launches"]),
+        "gpu_launches_per_step": round(t["launches"] / t["total_steps"], 3),
+        "numerics": {"check": "one timed-path batch per rank == cudaMemcpyAsync row fetch + fp32 PyTorch normalise/cast, bit for bit",
+                     "rows_checked": sum(n["rows"] for n in result["numerics"]), "mismatched_rows": bad,
+                     "max_abs_err": max(n["max_abs_err"] for n in result["numerics"])},
+        "numerics_ok": bad == 0 and finite,
+    })
+    if problems:
+        out["rejected"] = problems
+    return out
 
 
 def main():
@@ -271,6 +203,8 @@ def main():
     ap.add_argument("--e2e-tune", type=int, default=0)
     ap.add_argument("--host-threads", type=int, default=4)
     ap.add_argument("--host-stage", default="pull", choices=["gather", "memcpy", "pull"])
+    ap.add_argument("--min-seconds", type=float, default=1.0, help="minimum length of the device-timed region")
+    ap.add_argument("--e2e-min-seconds", type=float, default=0.5, help="minimum length of the e2e timed region")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

@@ -1,5 +1,6 @@
 """The other BASELINE.json configs through the public API (loader-only throughput, device-timed,
-max over ranks).  Launch with torch.distributed.run for N > 1.
+max over ranks; the timed region lasts >= --min-seconds, spans >= 2 window turnovers and ends after
+every fetch stream; one batch per rank is checked bit for bit against an independent fetch).  Launch with torch.distributed.run for N > 1.
 
   --config tensor10k   config 1: TensorDataset-like 10k x 3x32x32 fp32.  With DDL_B200_INSTANCES=1 and
                        2 processes this is the reference layout (1 DataPusher process + 1 consumer).
@@ -17,6 +18,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import ddl_b200 as ddl  # noqa: E402
+from ddl_b200.utils.benchmarking import check_numerics, timed_loop  # noqa: E402
 
 CONFIGS = {
     # name: (rows, nValues, dtype, batch, convert factory, splits)
@@ -62,6 +64,7 @@ def main():
     ap.add_argument("--instances", default="world")
     ap.add_argument("--storage", type=int, default=0, help="dedicated storage GPUs (producers:consumers = storage:rest)")
     ap.add_argument("--out", default=None)
+    ap.add_argument("--min-seconds", type=float, default=0.5)
     args = ap.parse_args()
     rows, nv, dtype, B, cvf, splits = CONFIGS[args.config]
     out = {}
@@ -69,40 +72,22 @@ def main():
     def body(env, conn):
         loader = ddl.DistributedDataLoader(Synthetic(rows, nv, dtype, cvf(), splits), B, conn, 10**9, 0.5,
                                            "sendrecv_replace", env.color, env.n_instances)
-        cuda = env.device.type == "cuda"
-
-        def batches():
-            while True:
-                for fields in loader:
-                    yield fields
-                    loader.mark(ddl.Marker.END_OF_BATCH)
-                loader.mark(ddl.Marker.END_OF_EPOCH)
-
-        it = batches()
-        for _ in range(args.warmup):
-            next(it)
-        if cuda:
-            torch.cuda.synchronize(env.device)
-        env.comm_nth_pusher.barrier()
-        t0 = time.perf_counter()
-        if cuda:
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-        for _ in range(args.steps):
-            x = next(it)
-        if cuda:
-            b.record()
-            torch.cuda.synchronize(env.device)
-        wall = (time.perf_counter() - t0) * 1e3
-        ms = a.elapsed_time(b) if cuda else wall
-        ms = max(env.comm_nth_pusher.allgather_obj(ms))
+        t = timed_loop(loader, env, args.steps, args.warmup, False, args.min_seconds, int(2.5 * (rows // B)),
+                       sample_clocks=env.comm_global.rank == 0)
+        nums = env.comm_global.allgather_obj(check_numerics(loader, t.pop("it")))
+        x = loader[0]
+        ms, steps = t["ms"], t["total_steps"]
         n = env.n_instances
         sample_bytes = nv * np.dtype(dtype).itemsize
         out.update(config=args.config, transport=env.transport, device=str(env.device.type), n_instances=n,
                    producers_per_instance=env.n_producers, storage_gpus=env.n_storage, batch_per_instance=B, sample_bytes=sample_bytes,
-                   out_dtype=str(x[0].dtype), ms_per_step=round(ms / args.steps, 4),
-                   samples_per_s=round(n * B * args.steps / ms * 1e3, 1),
-                   input_gbs=round(n * B * args.steps * sample_bytes / ms / 1e6, 1), rank=env.comm_global.rank)
+                   out_dtype=str(x[0].dtype), ms_per_step=round(ms / steps, 5),
+                   samples_per_s=round(n * B * steps / ms * 1e3, 1),
+                   input_gbs=round(n * B * steps * sample_bytes / ms / 1e6, 1), rank=env.comm_global.rank,
+                   steps=args.steps, repeats=t["repeats"], timed_region_s=round(ms * 1e-3, 4),
+                   windows_crossed=t["windows_crossed"], clocks=t["clocks"],
+                   mismatched_rows=sum(m["mismatched_rows"] for m in nums),
+                   rows_checked=sum(m["rows"] for m in nums))
         if args.config == "gpt2":
             out["tokens_per_s"] = round(out["samples_per_s"] * 1024)
         loader.close()

@@ -455,6 +455,30 @@ class DistributedDataLoader(DistributedDataloaderABC):
             self._checksum = BatchChecksum(self.device, self.batch_size, max(8, payload))
         return self._checksum.run(raw, payload)
 
+    def reference_batch(self) -> Tuple[torch.Tensor, ...]:
+        """The batch handed out last, rebuilt on an independent path: rows fetched one
+        ``cudaMemcpyAsync`` at a time from their owners' shards (no kernel of this library), then
+        converted by a plain PyTorch fp32 expression.  Must equal the delivered batch bit for bit;
+        benchmarks and tests use it as the numerics oracle on real multi-GPU runs (the reference
+        has no check of what a consumer received, reference tests/test_ddl.py:8-28)."""
+        if self._cur_slot < 0 or self.transport != "device":
+            raise RuntimeError("reference_batch needs a batch delivered by the device transport")
+        from .ops.gather import convert_reference
+
+        eng, k, B = self.engine, self.target_rank - 1, self.batch_size
+        buf = self.connection.pushers[k].lent_buf
+        first = self._cur_batch * B
+        if eng.cuda:
+            eng.side.synchronize()
+        slots = eng.tables[k, buf, first:first + B].cpu().numpy()
+        s = eng.specs[k]
+        raw = eng.reference_rows(k, slots)
+        lens = eng.batch_lengths(k, buf, first, B) if s.var else None
+        y = convert_reference(raw, s.convert, lens, copy_elem_size=s.np_dtype.itemsize)
+        if y.dtype != s.out_dtype:  # plain copies keep the window's own element type
+            y = y.view(s.out_dtype)
+        return torch.split(y[:, :s.nValues], list(s.splits), dim=1)
+
     def trace_summary(self) -> dict:
         """Device-time statistics per loader stage (needs ``LoaderConfig(trace=True)``)."""
         return self.engine.tracer.summary() if self.engine is not None else {}

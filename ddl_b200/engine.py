@@ -280,6 +280,7 @@ class DeviceEngine:
         n_sources = self.n_instances * self.P
         where = env.storage_rank_of if self.remote_storage else (lambda i: i)
         ptrs = [self.heap.peer_ptr(where(g // self.P), f"shard{g % self.P}_i{g // self.P}") for g in range(n_sources)]
+        self.src_ptrs = list(ptrs)  # this process's address of every shard (host address for host residency)
         self.plans: List = []
         self.stage = None
         if self.host_resident and config.host_stage in ("memcpy", "gather"):
@@ -634,6 +635,27 @@ class DeviceEngine:
         with torch.cuda.stream(stream):
             out = torch.cat([a, b])
         self.launches += 3
+        return out
+
+    def reference_rows(self, k: int, slots: np.ndarray) -> torch.Tensor:
+        """The raw bytes of the samples named by ``slots`` ([n, sample_bytes] uint8 on the engine's
+        device), fetched without any kernel of this library: one ``cudaMemcpyAsync`` per row from
+        the owning shard (peer mapping, local HBM or pinned host memory).  The independent half of
+        ``DistributedDataLoader.reference_batch``."""
+        s = self.specs[k]
+        slots = np.asarray(slots).astype(np.int64)
+        src, row = (slots >> SLOT_ROW_BITS) & 0xFFFF, slots & SLOT_ROW_MASK
+        if not self.cuda:
+            out = np.empty((slots.size, s.sample_bytes), dtype=np.uint8)
+            for i in range(slots.size):
+                out[i] = self.plans[k].shards[int(src[i])][int(row[i]), s.col_off:s.col_off + s.sample_bytes]
+            return torch.from_numpy(out)
+        out = torch.empty((slots.size, s.sample_bytes), dtype=torch.uint8, device=self.device)
+        st = torch.cuda.current_stream(self.device)
+        lib, sp = N.lib(), C.c_void_p(st.cuda_stream)
+        for i in range(slots.size):
+            a = self.src_ptrs[int(src[i])] + int(row[i]) * s.row_bytes + s.col_off
+            N.check(lib.bddl_memcpy_async(C.c_void_p(out[i].data_ptr()), C.c_void_p(a), s.sample_bytes, 4, sp))
         return out
 
     def on_lend(self, k: int, buf: int) -> None:

@@ -217,6 +217,37 @@ class GatherPlan:
             N.check(rc)
 
 
+def convert_reference(raw: torch.Tensor, convert: Convert, lengths: Optional[torch.Tensor] = None,
+                      copy_elem_size: int = 1) -> torch.Tensor:
+    """Plain PyTorch (fp32 math, separate multiply and add) statement of the conversion epilogue
+    on already gathered rows: ``raw`` is [n, sample_bytes] uint8 on any device, ``lengths`` the
+    valid elements per row of variable-size windows.  Returns [n, elems] in the output dtype."""
+    mode = convert.mode
+    n = raw.shape[0]
+    if mode == N.CVT_COPY:
+        y, pad = raw.clone(), int(convert.pad_value) & 0xFF
+    elif mode == N.CVT_I32_I64:
+        y, pad = raw.view(torch.int32).to(torch.int64), int(convert.pad_value)
+    else:
+        t = (raw if convert.in_elem_size == 1 else raw.view(torch.float32)).to(torch.float32)
+        n_elem, nch = t.shape[1], len(convert.scale)
+        if nch > 1 and convert.chan_stride > 0:
+            ch = (torch.arange(n_elem, device=raw.device) // convert.chan_stride) % nch
+            sc = torch.tensor(convert.scale, dtype=torch.float32, device=raw.device)[ch]
+            bi = torch.tensor(convert.bias, dtype=torch.float32, device=raw.device)[ch]
+        else:
+            sc = torch.tensor(convert.scale[0], dtype=torch.float32, device=raw.device)
+            bi = torch.tensor(convert.bias[0], dtype=torch.float32, device=raw.device)
+        y = t * sc
+        y = (y + bi).to(convert.out_dtype)
+        pad = convert.pad_value
+    if lengths is not None:
+        lengths = lengths.to(raw.device).long() * (copy_elem_size if mode == N.CVT_COPY else 1)  # copies pad bytes
+        mask = torch.arange(y.shape[1], device=raw.device)[None, :] >= lengths[:, None]
+        y[mask] = torch.tensor(pad, dtype=y.dtype, device=raw.device)
+    return y.view(n, -1)
+
+
 def gather_reference(shards: Sequence[np.ndarray], slots: np.ndarray, sample_bytes: int, convert: Convert,
                      lengths: Optional[Sequence[np.ndarray]] = None,
                      offsets: Optional[Sequence[np.ndarray]] = None) -> torch.Tensor:
