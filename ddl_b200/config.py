@@ -55,6 +55,9 @@ class LoaderConfig:
     verify: bool = False
     trace: bool = False            # CUDA-event timing of every loader stage
 
+    def __post_init__(self) -> None:
+        self.validate()  # also configs built directly (not through from_env) are checked
+
     @staticmethod
     def from_env(**overrides: Any) -> "LoaderConfig":
         vals: dict = {}
@@ -71,9 +74,7 @@ class LoaderConfig:
             else:
                 vals[f.name] = raw
         vals.update({k: v for k, v in overrides.items() if v is not None})
-        cfg = LoaderConfig(**vals)
-        cfg.validate()
-        return cfg
+        return LoaderConfig(**vals)
 
     def validate(self) -> None:
         if self.compat not in ("designed", "as_wired"):

@@ -248,13 +248,18 @@ class DistributedDataLoader(DistributedDataloaderABC):
             t0 = time.perf_counter()
             ev.synchronize()
             self.metrics.stall(time.perf_counter() - t0)
-        stream_wait(self.main, ev)
+        stream_wait(self._train_stream(), ev)  # whichever stream the training step runs on
         self._cur_slot, self._cur_batch = slot, b
         if self.cfg.prefetch:
             for d in range(1, self.cfg.prefetch_depth + 1):
                 if b + d < self.batches_per_window[k]:
                     self._prefetch(b + d)
         return self._batch_views(k, slot)
+
+    def _train_stream(self):
+        """The stream the user's step runs on *now* (``torch.cuda.stream(...)`` blocks, graph side
+        streams): the batch hand-over and the ring-slot release are ordered on it."""
+        return torch.cuda.current_stream(self.device) if self.cuda else self.main
 
     def _prefetch(self, b: int) -> None:
         if not self.cfg.prefetch or (self.transport == "process" and not self.cuda) or self._finalized:
@@ -369,12 +374,18 @@ class DistributedDataLoader(DistributedDataloaderABC):
             ev = self._consumed[self._cur_slot]
             if ev is None:
                 ev = self._consumed[self._cur_slot] = torch.cuda.Event()
-            ev.record(self.main)  # the "free" flag of this ring slot, in stream-event form
+            ts = self._train_stream()
+            ev.record(ts)  # the "free" flag of this ring slot, in stream-event form
             if self.engine is not None and self.engine.push:
-                self.engine.release_slot(self._cur_slot, self.main)
+                self.engine.release_slot(self._cur_slot, ts)
         self.batch += 1
         if self.batch % self.batches_per_window[self.target_rank - 1] == 0:
             self._window_done = True  # every batch of this epoch's window was delivered
+            if self.transport == "process" and self.cuda:
+                # the producer may overwrite the window the moment it is returned: every copy or
+                # zero-copy pull that still reads it must have finished on the device first
+                for fs in self.fetch_streams:
+                    fs.synchronize()
             self._end_access_epoch()
             self._advance_to_next_producer()
             self._start_access_epoch()

@@ -54,7 +54,9 @@ class NativeEvent:
 
     def record(self, stream=None) -> None:
         s = stream if stream is not None else torch.cuda.current_stream()
-        N.lib().bddl_event_record(self.handle, s.cuda_stream)
+        rc = N.lib().bddl_event_record(self.handle, s.cuda_stream)
+        if rc:
+            N.check(rc)
 
     def synchronize(self) -> None:
         N.check(N.lib().bddl_event_synchronize(self.handle))
@@ -69,7 +71,9 @@ class NativeEvent:
 def stream_wait(stream, ev) -> None:
     """``stream`` waits for ``ev``: native, torch or null events alike."""
     if isinstance(ev, NativeEvent):
-        N.lib().bddl_stream_wait_event(stream.cuda_stream, ev.handle)
+        rc = N.lib().bddl_stream_wait_event(stream.cuda_stream, ev.handle)
+        if rc:
+            N.check(rc)
     elif ev is not None:
         stream.wait_event(ev)
 

@@ -200,6 +200,7 @@ class Comm:
             name = "/bddl_sr_%x" % (abs(hash((base_s, os.getpid(), time.monotonic_ns()))) % (1 << 60))
             p = C.c_void_p()
             N.check(N.lib().bddl_shm_create(name.encode(), nbytes, C.byref(p)))
+            N.shm_created(name)  # unlinked at exit should this process die before the ack arrives
             C.memmove(p.value, buf.ctypes.data, nbytes)
             seg = (name, p.value)
             self.store.set(base_s, pickle.dumps(("shm", name, nbytes)))
@@ -237,6 +238,7 @@ class Comm:
 
             N.lib().bddl_shm_detach(C.c_void_p(seg[1]), nbytes)
             N.lib().bddl_shm_unlink(seg[0].encode())
+            N.shm_unlinked(seg[0])
 
     def _same_host(self, peer: int) -> bool:
         if not hasattr(self, "_hosts"):

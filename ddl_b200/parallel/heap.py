@@ -226,6 +226,12 @@ class SymmetricHeap:
             lib.bddl_ipc_close_handle(C.c_void_p(p))
         for p, n in self._attached:
             lib.bddl_shm_detach(C.c_void_p(p), n)
+        # freeing exported memory while a peer still holds it open is undefined (CUDA IPC): every
+        # rank closes its imports first, then all meet, then each frees what it exported
+        try:
+            self.comm.barrier()
+        except Exception:
+            pass
         for b in self.local.values():
             b._u8 = None
             if b._keep is not None and b._keep[0] == "pinned":

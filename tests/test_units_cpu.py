@@ -206,3 +206,15 @@ def test_public_names_match_the_reference():
     assert (r.nData, r.nValues, r.shape, r.splits) == (4, 2, (4, 2), (1, 1))
     with pytest.raises(NotImplementedError):
         ddl.ProducerFunctionSkeleton().execute_function()
+
+
+def test_config_built_directly_is_validated():
+    """A LoaderConfig that never went through from_env is checked too: ring_depth <= prefetch_depth
+    would let a prefetch overwrite the ring slot the training loop is still reading."""
+    import pytest
+
+    with pytest.raises(ValueError):
+        ddl.LoaderConfig(ring_depth=2, prefetch_depth=2)
+    with pytest.raises(ValueError):
+        ddl.LoaderConfig(exchange="teleport")
+    assert ddl.LoaderConfig(ring_depth=3, prefetch_depth=2).ring_depth == 3
