@@ -91,7 +91,7 @@ __global__ void flag_barrier_kernel(uint32_t* const* pages, int n_ranks, int me,
             __nanosleep(200);
         }
     }
-    if (st && status) atomicMax(status, st);
+    if (st && status) st_release_sys_u32(status, st);  // may be mapped host memory: no atomics
 }
 
 }  // namespace

@@ -47,7 +47,6 @@ struct KParams {
     uint32_t chunks_per_sample;
     uint32_t pad_bits;
     uint32_t col_off;               // byte offset of the delivered column slice inside a row
-    uint32_t filter_lo, filter_hi;  // push form: deliver only sources in [lo, hi); hi == 0 disables
     float scale[BDDL_MAX_CHANNELS];
     float bias[BDDL_MAX_CHANNELS];
 };
@@ -83,15 +82,11 @@ struct Item {
     uint32_t elem0;         // index of the chunk's first element inside the sample
 };
 
+// Work item (chunk c of batch row s) for the sample named by `slot`; `dst` is the batch tensor the
+// row belongs to (the consumer's own ring slot in the pull form, a peer's in the push form).
 template <int MODE, int CHUNK>
-__device__ __forceinline__ Item resolve_item(const KParams& p, uint32_t item) {
+__device__ __forceinline__ Item resolve_slot(const KParams& p, uint64_t slot, uint32_t s, uint32_t c, uint8_t* dst) {
     using C = Cvt<MODE>;
-    // chunk-major order: neighbouring warps work on the same chunk index of *different* samples,
-    // so a batch of few, huge samples still spreads its loads over all owners' NVLink ports
-    // instead of draining one owner at a time
-    const uint32_t c = item / p.n_samples;
-    const uint32_t s = item - c * p.n_samples;
-    const uint64_t slot = __ldg(p.slots + s);
     const uint32_t source = (uint32_t)(slot >> BDDL_SLOT_ROW_BITS);
     const uint64_t row = slot & kRowMask;
     const uint8_t* base = (const uint8_t*)__ldg((const unsigned long long*)(p.src_base + source));
@@ -109,14 +104,20 @@ __device__ __forceinline__ Item resolve_item(const KParams& p, uint32_t item) {
     Item it;
     it.in_bytes = len > start ? (uint32_t)min((int64_t)CHUNK, len - start) : 0u;
     it.region_bytes = (uint32_t)min((int64_t)CHUNK, p.sample_bytes - start);
-    if (p.filter_hi != 0 && (source < p.filter_lo || source >= p.filter_hi)) {
-        it.in_bytes = 0;  // another owner pushes this sample
-        it.region_bytes = 0;
-    }
     it.src = base + off + p.col_off + start;
     it.elem0 = (uint32_t)(start / C::IN_ES);
-    it.dst = p.dst + (int64_t)s * p.dst_row_bytes + (int64_t)it.elem0 * C::OUT_ES;
+    it.dst = dst + (int64_t)s * p.dst_row_bytes + (int64_t)it.elem0 * C::OUT_ES;
     return it;
+}
+
+template <int MODE, int CHUNK>
+__device__ __forceinline__ Item resolve_item(const KParams& p, uint32_t item) {
+    // chunk-major order: neighbouring warps work on the same chunk index of *different* samples,
+    // so a batch of few, huge samples still spreads its loads over all owners' NVLink ports
+    // instead of draining one owner at a time
+    const uint32_t c = item / p.n_samples;
+    const uint32_t s = item - c * p.n_samples;
+    return resolve_slot<MODE, CHUNK>(p, __ldg(p.slots + s), s, c, p.dst);
 }
 
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
@@ -292,6 +293,71 @@ __device__ __forceinline__ void convert_one(const KParams& p, const uint8_t* src
     }
 }
 
+// One output vector from PER input elements that all share one channel: no boundary logic at all.
+template <int MODE, bool G>
+__device__ __forceinline__ uint4 convert_group_uniform(const uint8_t* src, float sc, float no, float bi) {
+    using C = Cvt<MODE>;
+    uint4 out;
+    if constexpr (MODE == BDDL_CVT_COPY) {
+        out = ld16<G>(src);
+    } else if constexpr (MODE == BDDL_CVT_I32_I64) {
+        const uint2 v = ld8<G>(src);
+        const long long a = (int)v.x, b = (int)v.y;
+        out.x = (uint32_t)a;
+        out.y = (uint32_t)((unsigned long long)a >> 32);
+        out.z = (uint32_t)b;
+        out.w = (uint32_t)((unsigned long long)b >> 32);
+    } else {
+        float f[C::PER];
+        if constexpr (C::IN_ES == 1) {
+            if constexpr (C::PER == 8) {
+                const uint2 v = ld8<G>(src);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    f[k] = affine_u8(u8_magic(v.x, k), sc, no, bi);
+                    f[4 + k] = affine_u8(u8_magic(v.y, k), sc, no, bi);
+                }
+            } else {
+                const uint32_t v = ld4<G>(src);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) f[k] = affine_u8(u8_magic(v, k), sc, no, bi);
+            }
+        } else {
+            const uint4 a = ld16<G>(src);
+            const uint4 b = ld16<G>(src + 16);
+            f[0] = affine(__uint_as_float(a.x), sc, bi), f[1] = affine(__uint_as_float(a.y), sc, bi);
+            f[2] = affine(__uint_as_float(a.z), sc, bi), f[3] = affine(__uint_as_float(a.w), sc, bi);
+            f[4] = affine(__uint_as_float(b.x), sc, bi), f[5] = affine(__uint_as_float(b.y), sc, bi);
+            f[6] = affine(__uint_as_float(b.z), sc, bi), f[7] = affine(__uint_as_float(b.w), sc, bi);
+        }
+        if constexpr (C::OUT_ES == 2) {
+            out.x = pack_bf16(f[0], f[1]);
+            out.y = pack_bf16(f[2], f[3]);
+            out.z = pack_bf16(f[4], f[5]);
+            out.w = pack_bf16(f[6], f[7]);
+        } else {
+            out.x = __float_as_uint(f[0]);
+            out.y = __float_as_uint(f[1]);
+            out.z = __float_as_uint(f[2]);
+            out.w = __float_as_uint(f[3]);
+        }
+    }
+    return out;
+}
+
+// Groups [g0, g1) of a chunk, one channel: the hot loop (per 8 pixels of the uint8 -> bf16 form:
+// one LDS.64, 8 PRMT, 8 FFMA, 8 FADD, 4 packs, one STG.128; 32-bit index arithmetic).
+template <int MODE, bool G, int UNROLL>
+__device__ __forceinline__ void convert_span(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, uint32_t g0,
+                                             uint32_t g1, int lane, float sc, float no, float bi) {
+    using C = Cvt<MODE>;
+#pragma unroll UNROLL
+    for (uint32_t g = g0 + lane; g < g1; g += 32) {
+        const uint4 v = convert_group_uniform<MODE, G>(src + g * (uint32_t)(C::PER * C::IN_ES), sc, no, bi);
+        *reinterpret_cast<uint4*>(dst + g * 16u) = v;
+    }
+}
+
 // Convert the payload of one chunk (src: shared or global) and pad the rest of its region.
 template <int MODE, bool CHAN, bool G, int UNROLL, uint32_t CHUNK_ELEMS>
 __device__ __forceinline__ void convert_chunk(const KParams& p, const uint8_t* __restrict__ src,
@@ -301,11 +367,30 @@ __device__ __forceinline__ void convert_chunk(const KParams& p, const uint8_t* _
     const uint32_t n_elems = it.in_bytes / C::IN_ES;
     const uint32_t n_groups = n_elems / C::PER;
     const ChanCtx cx = make_ctx<CHAN>(p, it.elem0, CHUNK_ELEMS);
+    if (!CHAN || cx.fast) {
+        // a chunk touches at most two channels: [0, gb) is the first, the group that straddles the
+        // boundary (if any) goes through the per-element selects, the rest is the second channel
+        const uint32_t gb = CHAN ? min(n_groups, cx.boundary / (uint32_t)C::PER) : n_groups;
+        convert_span<MODE, G, UNROLL>(src, dst, 0, gb, lane, cx.sc0, cx.no0, cx.bi0);
+        if (CHAN && gb < n_groups) {
+            uint32_t g2 = gb;
+            if (cx.boundary % (uint32_t)C::PER) {
+                if (lane == 0) {
+                    const uint4 v = convert_group<MODE, CHAN, G>(p, cx, src + gb * (uint32_t)(C::PER * C::IN_ES),
+                                                                 gb * C::PER, it.elem0 + gb * C::PER);
+                    *reinterpret_cast<uint4*>(dst + gb * 16u) = v;
+                }
+                g2 = gb + 1;
+            }
+            convert_span<MODE, G, UNROLL>(src, dst, g2, n_groups, lane, cx.sc1, cx.no1, cx.bi1);
+        }
+    } else {
 #pragma unroll UNROLL
-    for (uint32_t g = lane; g < n_groups; g += 32) {
-        const uint4 v = convert_group<MODE, CHAN, G>(p, cx, src + (size_t)g * (C::PER * C::IN_ES), g * C::PER,
-                                                     it.elem0 + g * C::PER);
-        *reinterpret_cast<uint4*>(dst + (size_t)g * 16) = v;
+        for (uint32_t g = lane; g < n_groups; g += 32) {
+            const uint4 v = convert_group<MODE, CHAN, G>(p, cx, src + (size_t)g * (C::PER * C::IN_ES), g * C::PER,
+                                                         it.elem0 + g * C::PER);
+            *reinterpret_cast<uint4*>(dst + (size_t)g * 16) = v;
+        }
     }
     const uint32_t done = n_groups * C::PER;
     for (uint32_t e = done + lane; e < n_elems; e += 32)
@@ -338,6 +423,41 @@ __global__ void __launch_bounds__(kWarps * 32) gather_ldg_kernel(const __grid_co
 }
 
 // ---- TMA / convert form ------------------------------------------------------------------------
+// One warp's pipeline over its private ring of STAGES chunks: lane 0 keeps STAGES bulk loads in
+// flight, the warp converts a landed stage straight into the batch tensor and re-arms the stage.
+// item_at(k) names the warp's k-th work item.
+template <int MODE, bool CHAN, int CHUNK, int STAGES, typename ItemAt>
+__device__ __forceinline__ void warp_pipeline(const KParams& p, uint8_t* ring, uint64_t* full, uint32_t n_my,
+                                              int lane, ItemAt item_at) {
+    auto issue = [&](uint32_t k) {
+        const Item it = item_at(k);
+        if (it.in_bytes == 0) return;
+        const int s = k % STAGES;
+        const uint32_t bytes = (it.in_bytes + 15u) & ~15u;
+        mbar_arrive_expect_tx(full + s, bytes);
+        bulk_g2s(ring + (size_t)s * CHUNK, it.src, bytes, full + s);
+    };
+
+    if (lane == 0)
+        for (uint32_t k = 0; k < min(n_my, (uint32_t)STAGES); ++k) issue(k);
+
+    uint32_t phase = 0;  // one parity bit per stage
+    for (uint32_t k = 0; k < n_my; ++k) {
+        const int s = k % STAGES;
+        const Item it = item_at(k);
+        if (it.in_bytes != 0) {
+            mbar_wait(full + s, (phase >> s) & 1u);
+            phase ^= 1u << s;
+        }
+        convert_chunk<MODE, CHAN, false, 4, CHUNK / Cvt<MODE>::IN_ES>(p, ring + (size_t)s * CHUNK, it, lane);
+        __syncwarp();
+        if (lane == 0 && k + STAGES < n_my) {
+            fence_proxy_async_smem();  // the warp's reads of this stage precede the next bulk write
+            issue(k + STAGES);
+        }
+    }
+}
+
 template <int MODE, bool CHAN, int CHUNK, int STAGES, int NW>
 __global__ void __launch_bounds__(NW * 32) gather_tma_cvt_kernel(const __grid_constant__ KParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -356,34 +476,138 @@ __global__ void __launch_bounds__(NW * 32) gather_tma_cvt_kernel(const __grid_co
     const uint32_t gw = blockIdx.x * NW + warp;
     const uint32_t nw = gridDim.x * NW;
     const uint32_t n_my = gw < p.n_items ? (p.n_items - gw + nw - 1) / nw : 0;
+    warp_pipeline<MODE, CHAN, CHUNK, STAGES>(p, ring, full, n_my, lane,
+                                             [&](uint32_t k) { return resolve_item<MODE, CHUNK>(p, gw + k * nw); });
+}
 
-    auto issue = [&](uint32_t k) {
-        const Item it = resolve_item<MODE, CHUNK>(p, gw + k * nw);
-        if (it.in_bytes == 0) return;
-        const int s = k % STAGES;
-        const uint32_t bytes = (it.in_bytes + 15u) & ~15u;
-        mbar_arrive_expect_tx(full + s, bytes);
-        bulk_g2s(ring + (size_t)s * CHUNK, it.src, bytes, full + s);
-    };
+// ---- push form ---------------------------------------------------------------------------------
+// The "DataPusher" direction (reference ddl/datapusher.py:147-170 offers a window, the consumer
+// reads it): here the OWNER of a sample delivers it.  One launch per loader step on every GPU:
+// the grid is cut into one group of CTAs per consumer; a group
+//   1. waits (bounded) until that consumer has released the ring slot (`free` word, written by the
+//      consumer's training stream) and published the slot table of the window (`table` word),
+//   2. copies the consumer's slice of its slot table into shared memory (one NVLink read) and
+//      keeps the samples this GPU owns,
+//   3. runs the same per-warp TMA pipeline as the pull form -- bulk loads from the LOCAL shard,
+//      conversion, 16-byte stores into the consumer's ring slot through its peer mapping (posted
+//      NVLink writes), and
+//   4. the last CTA of the group to finish adds 1 to the consumer's `ready` word with
+//      red.release.sys after a system-scope fence: the hand-over token of the reference
+//      (ddl/connection.py:153-182) is written from inside the kernel that moved the data.
+// CTA 0 finally waits (bounded) until all owners have bumped this GPU's own `ready` word, so the
+// kernel's completion *is* "my batch is assembled" and the loader needs no second launch.
+struct PushParams {
+    const uint64_t* const* tables;  // [n_ranks] every consumer's slot-table buffer (peer mappings)
+    uint8_t* const* rings;          // [n_ranks] every consumer's batch ring (peer mappings)
+    uint32_t* const* flags;         // [n_ranks] every rank's flag page (peer mappings)
+    int64_t table_off;              // byte offset of the window slice inside a table buffer
+    int64_t ring_off;               // byte offset of the ring slot inside a ring
+    unsigned long long max_polls;
+    uint32_t* status;               // 0 ok, 1 timed out, 2 stopped
+    int32_t n_ranks, me, ctas_per_consumer;
+    uint32_t owner_lo, owner_hi;    // source ids this GPU owns
+    uint32_t ready_word, free_word0, table_word0, done_word0, stop_word;
+    uint32_t free_need, table_need, ready_need, done_target;
+};
 
-    if (lane == 0)
-        for (uint32_t k = 0; k < min(n_my, (uint32_t)STAGES); ++k) issue(k);
+__device__ __forceinline__ uint32_t poll_geq(const uint32_t* flag, uint32_t need, const uint32_t* stop,
+                                             unsigned long long max_polls) {
+    unsigned long long polls = 0;
+    while ((int32_t)(ld_acquire_sys_u32(flag) - need) < 0) {
+        if (ld_acquire_sys_u32(stop) != 0) return 2;
+        if (++polls >= max_polls) return 1;
+        __nanosleep(200);
+    }
+    return 0;
+}
 
-    uint32_t phase = 0;  // one parity bit per stage
-    for (uint32_t k = 0; k < n_my; ++k) {
-        const int s = k % STAGES;
-        const Item it = resolve_item<MODE, CHUNK>(p, gw + k * nw);
-        if (it.in_bytes != 0) {
-            mbar_wait(full + s, (phase >> s) & 1u);
-            phase ^= 1u << s;
+template <int MODE, bool CHAN, int CHUNK, int STAGES, int NW>
+__global__ void __launch_bounds__(NW * 32) push_tma_cvt_kernel(const __grid_constant__ KParams p,
+                                                               const __grid_constant__ PushParams q) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    uint8_t* ring = smem + (size_t)warp * STAGES * CHUNK;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)NW * STAGES * CHUNK) + warp * STAGES;
+    uint32_t* ctrl = reinterpret_cast<uint32_t*>(smem + (size_t)NW * STAGES * CHUNK + (size_t)NW * STAGES * 8);
+    uint64_t* slot_of = reinterpret_cast<uint64_t*>(ctrl + 4);         // [n_samples] the consumer's slice
+    uint16_t* mine = reinterpret_cast<uint16_t*>(slot_of + p.n_samples);  // batch rows this GPU owns
+
+    const int G = q.ctas_per_consumer;
+    const int group = blockIdx.x / G;
+    const int lc = blockIdx.x - group * G;
+    const int c = (q.me + group) % q.n_ranks;  // staggered: owners do not all start on one consumer
+    uint32_t* my_page = q.flags[q.me];
+    const uint32_t* stop = my_page + q.stop_word;
+
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(full + s, 1);
+        fence_mbar_init();
+    }
+    if (threadIdx.x == 0) {
+        uint32_t st = 0;
+        // status = outcome (1 timed out, 2 stopped) | which wait (1 free, 2 table, 3 ready) << 4 | peer << 8
+        if (q.free_need) st = poll_geq(my_page + q.free_word0 + c, q.free_need, stop, q.max_polls);
+        if (st) st |= (1u << 4) | ((uint32_t)c << 8);
+        if (!st) {
+            st = poll_geq(my_page + q.table_word0 + c, q.table_need, stop, q.max_polls);
+            if (st) st |= (2u << 4) | ((uint32_t)c << 8);
         }
-        convert_chunk<MODE, CHAN, false, 2, CHUNK / Cvt<MODE>::IN_ES>(p, ring + (size_t)s * CHUNK, it, lane);
-        __syncwarp();
-        if (lane == 0 && k + STAGES < n_my) {
-            fence_proxy_async_smem();  // the warp's reads of this stage precede the next bulk write
-            issue(k + STAGES);
+        ctrl[0] = st;
+    }
+    __syncthreads();
+    uint32_t st = ctrl[0];
+    if (st == 0) {
+        const uint64_t* theirs = reinterpret_cast<const uint64_t*>(reinterpret_cast<const uint8_t*>(q.tables[c]) +
+                                                                   q.table_off);
+        for (uint32_t i = threadIdx.x; i < p.n_samples; i += NW * 32) slot_of[i] = __ldcg(theirs + i);
+        __syncthreads();
+        if (warp == 0) {  // ordered compaction: every CTA of the group builds the identical list
+            uint32_t n = 0;
+            for (uint32_t b = 0; b < p.n_samples; b += 32) {
+                const uint32_t i = b + lane;
+                bool own = false;
+                if (i < p.n_samples) {
+                    const uint32_t source = (uint32_t)(slot_of[i] >> BDDL_SLOT_ROW_BITS);
+                    own = source >= q.owner_lo && source < q.owner_hi;
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, own);
+                if (own) mine[n + __popc(m & ((1u << lane) - 1u))] = (uint16_t)i;
+                n += __popc(m);
+            }
+            if (lane == 0) ctrl[1] = n;
+        }
+        __syncthreads();
+        const uint32_t n_mine = ctrl[1];
+        const uint32_t n_items = n_mine * p.chunks_per_sample;
+        const uint32_t gw = lc * NW + warp;
+        const uint32_t nw = G * NW;
+        const uint32_t n_my = gw < n_items ? (n_items - gw + nw - 1) / nw : 0;
+        uint8_t* dst = q.rings[c] + q.ring_off;
+        warp_pipeline<MODE, CHAN, CHUNK, STAGES>(p, ring, full, n_my, lane, [&](uint32_t k) {
+            const uint32_t item = gw + k * nw;
+            const uint32_t ch = item / n_mine;
+            const uint32_t s = mine[item - ch * n_mine];
+            return resolve_slot<MODE, CHUNK>(p, slot_of[s], s, ch, dst);
+        });
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence_system();  // this CTA's stores into the consumer's ring are visible system-wide
+            const uint32_t t = atomicAdd(my_page + q.done_word0 + c, 1u) + 1u;
+            if (t == q.done_target) {  // last CTA of the group: every CTA's stores precede the token
+                __threadfence_system();
+                red_release_sys_add_u32(q.flags[c] + q.ready_word, 1u);
+            }
         }
     }
+    // status may live in mapped host memory (the loader reads it without synchronising): a plain
+    // release store; any non-zero value says that a bounded wait gave up
+    if (blockIdx.x == 0 && threadIdx.x == 0 && st == 0) {
+        st = poll_geq(my_page + q.ready_word, q.ready_need, stop, q.max_polls);
+        if (st) st |= (3u << 4) | ((uint32_t)q.me << 8);
+    }
+    if (st && threadIdx.x == 0) st_release_sys_u32(q.status, st);
 }
 
 // ---- TMA / copy form ---------------------------------------------------------------------------
@@ -544,25 +768,49 @@ int launch_mode(const bddl_gather_desc* d, KParams& p, bool tma, cudaStream_t st
     }
 }
 
+template <int MODE, bool CHAN>
+int launch_push(const bddl_gather_desc* d, KParams& p, PushParams& q, cudaStream_t st) {
+    constexpr int CHUNK = 4096, STAGES = 3, NW = 16;
+    const size_t smem = (size_t)NW * STAGES * CHUNK + (size_t)NW * STAGES * sizeof(uint64_t) + 16 +
+                        (size_t)d->n_samples * (sizeof(uint64_t) + sizeof(uint16_t));
+    if (smem > 227 * 1024)
+        return bddl_fail(BDDL_ERR_UNSUPPORTED, "push: %d samples per batch exceed the kernel's slot list (%d at most)",
+                         d->n_samples, (int)((227 * 1024 - (size_t)NW * STAGES * (CHUNK + 8) - 16) / 10));
+    static bool configured[64];
+    int dev = 0;
+    BDDL_CUDA(cudaGetDevice(&dev));
+    auto kernel = push_tma_cvt_kernel<MODE, CHAN, CHUNK, STAGES, NW>;
+    if (!configured[dev & 63]) {
+        int rc = set_smem(kernel, 227 * 1024);
+        if (rc) return rc;
+        configured[dev & 63] = true;
+    }
+    p.chunks_per_sample = chunks_for<CHUNK>(d->sample_bytes);
+    p.n_items = (uint32_t)d->n_samples * p.chunks_per_sample;
+    kernel<<<q.n_ranks * q.ctas_per_consumer, NW * 32, smem, st>>>(p, q);
+    bddl_count_launch(1);
+    BDDL_CUDA(cudaGetLastError());
+    return 0;
+}
+
 }  // namespace
 
 static int64_t g_launches = 0;
 void bddl_count_launch(int64_t n) { __atomic_fetch_add(&g_launches, n, __ATOMIC_RELAXED); }
 extern "C" int64_t bddl_launch_count(void) { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
-extern "C" int bddl_exchange_gather_collate(const bddl_gather_desc* d, void* stream) {
-    if (!d) return bddl_fail(BDDL_ERR_INVALID, "gather: null descriptor");
-    if (d->n_samples == 0) return 0;
-    if (!d->d_src_base || !d->d_slots || !d->d_dst || d->n_samples < 0 || d->n_sources < 1)
+// Validate a descriptor and translate it into kernel parameters (slots / dst are checked by the callers).
+static int build_params(const bddl_gather_desc* d, KParams& p, bool& chan, bool& var) {
+    if (!d->d_src_base || d->n_samples < 0 || d->n_sources < 1)
         return bddl_fail(BDDL_ERR_INVALID, "gather: null pointer or bad counts");
     if (d->mode < BDDL_CVT_COPY || d->mode > BDDL_CVT_I32_I64)
         return bddl_fail(BDDL_ERR_INVALID, "gather: unknown conversion mode %d", d->mode);
     if (d->sample_bytes <= 0 || d->sample_bytes >= (1LL << 31))
         return bddl_fail(BDDL_ERR_INVALID, "gather: sample_bytes %lld out of range", (long long)d->sample_bytes);
-    if ((d->dst_row_bytes & 15) || ((uintptr_t)d->d_dst & 15))
+    if (d->dst_row_bytes & 15)
         return bddl_fail(BDDL_ERR_INVALID, "gather: batch rows must be 16-byte aligned (stride %lld)",
                          (long long)d->dst_row_bytes);
-    const bool var = d->d_src_offsets != nullptr;
+    var = d->d_src_offsets != nullptr;
     if (var && !d->d_src_lengths) return bddl_fail(BDDL_ERR_INVALID, "gather: offsets without lengths");
     if (d->col_offset_bytes < 0 || (d->col_offset_bytes & 15) || (var && d->col_offset_bytes))
         return bddl_fail(BDDL_ERR_INVALID, "gather: col_offset_bytes must be a non-negative multiple of 16 (fixed-size rows)");
@@ -576,10 +824,9 @@ extern "C" int bddl_exchange_gather_collate(const bddl_gather_desc* d, void* str
     if (d->dst_row_bytes < ((out_bytes + 15) & ~15LL))
         return bddl_fail(BDDL_ERR_INVALID, "gather: dst_row_bytes %lld too small for %lld output bytes",
                          (long long)d->dst_row_bytes, (long long)out_bytes);
-    const bool chan = d->n_channels > 1 && d->chan_stride > 0;
+    chan = d->n_channels > 1 && d->chan_stride > 0;
     if (d->n_channels > BDDL_MAX_CHANNELS) return bddl_fail(BDDL_ERR_INVALID, "gather: too many channels");
 
-    KParams p;
     p.src_base = d->d_src_base;
     p.src_offsets = d->d_src_offsets;
     p.src_lengths = d->d_src_lengths;
@@ -593,12 +840,22 @@ extern "C" int bddl_exchange_gather_collate(const bddl_gather_desc* d, void* str
     p.pad_bits = d->pad_bits;
     p.n_samples = (uint32_t)d->n_samples;
     p.col_off = (uint32_t)d->col_offset_bytes;
-    p.filter_lo = (uint32_t)d->filter_lo;
-    p.filter_hi = (uint32_t)d->filter_hi;
     for (int i = 0; i < BDDL_MAX_CHANNELS; ++i) {
         p.scale[i] = d->scale[i];
         p.bias[i] = d->bias[i];
     }
+    return 0;
+}
+
+extern "C" int bddl_exchange_gather_collate(const bddl_gather_desc* d, void* stream) {
+    if (!d) return bddl_fail(BDDL_ERR_INVALID, "gather: null descriptor");
+    if (d->n_samples == 0) return 0;
+    if (!d->d_slots || !d->d_dst || ((uintptr_t)d->d_dst & 15))
+        return bddl_fail(BDDL_ERR_INVALID, "gather: null slots/dst or unaligned dst");
+    KParams p;
+    bool chan, var;
+    int rc = build_params(d, p, chan, var);
+    if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
 
     bool tma;
@@ -611,7 +868,7 @@ extern "C" int bddl_exchange_gather_collate(const bddl_gather_desc* d, void* str
 
     switch (d->mode) {
         case BDDL_CVT_COPY:
-            if (tma && !var && d->filter_hi == 0) {
+            if (tma && !var) {
                 switch (d->tune) {
                     case 1:
                         return launch_tma_copy<4096, 6>(d, p, st);
@@ -645,4 +902,66 @@ extern "C" int bddl_gather_step(const bddl_gather_desc* d, void* stream, void* w
     if (rc) return rc;
     if (record_event) BDDL_CUDA(cudaEventRecord((cudaEvent_t)record_event, st));
     return 0;
+}
+
+// CTAs per consumer group of the push kernel for `n_ranks` ranks and an SM budget (0 = all SMs).
+extern "C" int bddl_push_ctas_per_consumer(int32_t n_ranks, int32_t max_ctas, int32_t* out) {
+    if (n_ranks < 1 || !out) return bddl_fail(BDDL_ERR_INVALID, "push: bad arguments");
+    int sms = 0;
+    int rc = sm_count(&sms);
+    if (rc) return rc;
+    const int cap = max_ctas > 0 ? max_ctas : sms;
+    *out = cap / n_ranks > 0 ? cap / n_ranks : 1;
+    return 0;
+}
+
+extern "C" int bddl_exchange_push_collate(const bddl_gather_desc* d, const bddl_push_desc* u, void* stream) {
+    if (!d || !u) return bddl_fail(BDDL_ERR_INVALID, "push: null descriptor");
+    if (d->n_samples <= 0 || d->n_samples > 65535) return bddl_fail(BDDL_ERR_INVALID, "push: 1..65535 samples per batch");
+    if (!u->d_tables || !u->d_rings || !u->d_flags || !u->d_status || u->n_ranks < 1 ||
+        u->n_ranks > BDDL_FLAG_MAX_RANKS || u->me < 0 || u->me >= u->n_ranks || u->ring_slot < 0 ||
+        u->ring_slot >= BDDL_FLAG_MAX_SLOTS || u->window < 0 || u->window >= BDDL_FLAG_MAX_WINDOWS ||
+        u->ctas_per_consumer < 1 || (u->ring_offset_bytes & 15) || (u->table_offset_bytes & 7))
+        return bddl_fail(BDDL_ERR_INVALID, "push: bad descriptor");
+    KParams p;
+    bool chan, var;
+    int rc = build_params(d, p, chan, var);
+    if (rc) return rc;
+    p.slots = nullptr;
+    p.dst = nullptr;
+    PushParams q;
+    q.tables = (const uint64_t* const*)u->d_tables;
+    q.rings = (uint8_t* const*)u->d_rings;
+    q.flags = (uint32_t* const*)u->d_flags;
+    q.table_off = u->table_offset_bytes;
+    q.ring_off = u->ring_offset_bytes;
+    q.max_polls = u->max_polls ? u->max_polls : ~0ULL;
+    q.status = u->d_status;
+    q.n_ranks = u->n_ranks;
+    q.me = u->me;
+    q.ctas_per_consumer = u->ctas_per_consumer;
+    q.owner_lo = (uint32_t)u->owner_lo;
+    q.owner_hi = (uint32_t)u->owner_hi;
+    q.ready_word = BDDL_FLAG_READY0 + u->ring_slot;
+    q.free_word0 = BDDL_FLAG_FREE0 + u->ring_slot * BDDL_FLAG_MAX_RANKS;
+    q.done_word0 = BDDL_FLAG_DONE0 + u->ring_slot * BDDL_FLAG_MAX_RANKS;
+    q.table_word0 = BDDL_FLAG_TABLE0 + u->window * BDDL_FLAG_MAX_RANKS;
+    q.stop_word = BDDL_FLAG_STOP;
+    q.free_need = u->use;  // the slot's previous contents (its use-th fill) have been consumed
+    q.table_need = u->table_seq;
+    q.ready_need = (u->use + 1) * (uint32_t)u->n_ranks;  // every owner bumps `ready` once per fill
+    q.done_target = (u->use + 1) * (uint32_t)u->ctas_per_consumer;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (d->mode) {
+        case BDDL_CVT_COPY:
+            return launch_push<BDDL_CVT_COPY, false>(d, p, q, st);
+        case BDDL_CVT_U8_BF16:
+            return chan ? launch_push<BDDL_CVT_U8_BF16, true>(d, p, q, st) : launch_push<BDDL_CVT_U8_BF16, false>(d, p, q, st);
+        case BDDL_CVT_F32_BF16:
+            return chan ? launch_push<BDDL_CVT_F32_BF16, true>(d, p, q, st) : launch_push<BDDL_CVT_F32_BF16, false>(d, p, q, st);
+        case BDDL_CVT_U8_F32:
+            return chan ? launch_push<BDDL_CVT_U8_F32, true>(d, p, q, st) : launch_push<BDDL_CVT_U8_F32, false>(d, p, q, st);
+        default:
+            return launch_push<BDDL_CVT_I32_I64, false>(d, p, q, st);
+    }
 }

@@ -34,8 +34,12 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
     return ok != 0;
 }
 
+// Bounded: a bulk load whose bytes never arrive (a peer that went away) ends the kernel with a
+// trap -- a loud launch failure on the host -- instead of spinning forever.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
+        if (++spins > (1u << 26)) __trap();
     }
 }
 

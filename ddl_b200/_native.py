@@ -69,10 +69,38 @@ class GatherDesc(C.Structure):
         ("pad_bits", C.c_uint32),
         ("variant", C.c_int32),
         ("max_ctas", C.c_int32),
-        ("filter_lo", C.c_int32),
-        ("filter_hi", C.c_int32),
+        ("reserved0", C.c_int32),
+        ("reserved1", C.c_int32),
         ("col_offset_bytes", C.c_int32),
         ("tune", C.c_int32),
+    ]
+
+
+# flag page layout of the device transport (mirror of the BDDL_FLAG_* constants)
+FLAG_PAGE_BYTES, FLAG_MAX_RANKS, FLAG_MAX_SLOTS, FLAG_MAX_WINDOWS = 16384, 64, 16, 24
+FLAG_BARRIER0, FLAG_READY0, FLAG_STOP, FLAG_FREE0, FLAG_DONE0, FLAG_TABLE0 = 0, 256, 272, 512, 1536, 2560
+
+
+class PushDesc(C.Structure):
+    """Mirror of ``bddl_push_desc``."""
+
+    _fields_ = [
+        ("d_tables", C.c_void_p),
+        ("d_rings", C.c_void_p),
+        ("d_flags", C.c_void_p),
+        ("table_offset_bytes", C.c_int64),
+        ("ring_offset_bytes", C.c_int64),
+        ("max_polls", C.c_uint64),
+        ("d_status", C.c_void_p),
+        ("n_ranks", C.c_int32),
+        ("me", C.c_int32),
+        ("ring_slot", C.c_int32),
+        ("window", C.c_int32),
+        ("owner_lo", C.c_int32),
+        ("owner_hi", C.c_int32),
+        ("ctas_per_consumer", C.c_int32),
+        ("use", C.c_uint32),
+        ("table_seq", C.c_uint32),
     ]
 
 
@@ -99,9 +127,12 @@ def _declare(lib: C.CDLL) -> None:
         "bddl_host_shuffle_i32": (C.c_int, [P(RngState), vp, i64]),
         "bddl_host_shuffle_rows": (C.c_int, [P(RngState), vp, i64, i64]),
         "bddl_partner_select": (C.c_int, [P(RngState), i32, i32, P(i32), P(i32), vp, P(i32)]),
-        "bddl_perm_gen": (C.c_int, [vp, i64, i64, vp, i32, vp]),
+        "bddl_perm_gen": (C.c_int, [vp, i64, i64, vp, i32, vp, i64, vp]),
+        "bddl_perm_gen_scratch_bytes": (i64, [i64]),
         "bddl_exchange_gather_collate": (C.c_int, [P(GatherDesc), vp]),
         "bddl_launch_count": (i64, []),
+        "bddl_push_ctas_per_consumer": (C.c_int, [i32, i32, P(i32)]),
+        "bddl_exchange_push_collate": (C.c_int, [P(GatherDesc), P(PushDesc), vp]),
     }
     sz = C.c_size_t
     sigs.update({

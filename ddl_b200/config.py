@@ -33,11 +33,10 @@ class LoaderConfig:
     gather_variant: int = 0        # BDDL_VARIANT_*
     gather_tune: int = 0
     gather_max_ctas: int = 0       # SM budget of the batch-assembly kernel (0 = all SMs)
-    exchange: str = "pull"         # pull | push
-    # push form: how a stream waits for a counter.  "kernel" = one-thread bounded acquire-poll
-    # kernel; "stream" = cuStreamWaitValue32 (no SM, but a blocked wait sits at the head of its
-    # hardware queue and can hold back unrelated streams that share the queue)
-    push_wait: str = "stream"
+    # pull: each consumer's kernel loads its samples from their owners (no cross-GPU hand-over per
+    # step).  push: each owner's kernel stores the samples it owns into every consumer's ring slot
+    # and signals `ready` from inside the kernel; all consumers must step in lock-step.
+    exchange: str = "pull"
     host_pull: bool = False        # process transport: kernel reads the pinned window directly
     residency: str = "hbm"         # device transport: shards in "hbm" or in pinned "host" memory
     # host residency: "gather" (threaded CPU gather into a pinned buffer + one cudaMemcpyAsync),

@@ -297,7 +297,8 @@ class DistributedDataLoader(DistributedDataloaderABC):
                 with eng.tracer.span("gather", stream):
                     eng.gather(k, self.connection.pushers[k].lent_buf, b * B, slot, stream=stream)
             elif eng.push:
-                eng.push_step(k, self.connection.pushers[k].lent_buf, b * B, slot, stream)
+                pusher = self.connection.pushers[k]
+                eng.push_step(k, pusher.lent_buf, b * B, slot, stream, pusher.lent_seq)
             else:
                 eng.gather(k, self.connection.pushers[k].lent_buf, b * B, slot, stream=stream)
             if self.cfg.verify and eng.cuda and not eng.push and eng.stage is None:

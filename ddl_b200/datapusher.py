@@ -231,6 +231,9 @@ class DevicePusher:
         self.mode = "device"
         self.iterations = 0
         self._ready = None        # (table buffer, event) of the newest produced iteration
+        self._produce_seq = 0     # tables produced so far (never rewound: the push form's `table` word)
+        self._ready_seq = 0
+        self.lent_seq = 0
         self._returned_ev = None  # consumer finished reading the previous iteration
         self.lent_buf = 0
         self._stopped = False
@@ -294,9 +297,14 @@ class DevicePusher:
                 self._produce_body(eng, k)
         else:
             self._produce_body(eng, k)
+        self._produce_seq += 1
+        if eng.push:
+            # owners on other GPUs read this table from inside their push kernels: publish its number
+            eng.signal_table_ready(k, self._produce_seq)
         ev = eng.event()
         ev.record(eng.side) if eng.cuda else None
         self._ready = (eng.cur[k], ev)
+        self._ready_seq = self._produce_seq
         self.iterations += 1
 
     def _produce_body(self, eng, k) -> None:
@@ -341,6 +349,7 @@ class DevicePusher:
         for st in eng.fetch_streams:
             eng.wait(st, ev)
         self.lent_buf = buf
+        self.lent_seq = self._ready_seq
         eng.on_lend(self.k, buf)
         if self.run_ahead and not self._stopped:
             self.produce()

@@ -257,7 +257,7 @@ class DeviceEngine:
             self.shards = [self.heap.alloc(f"shard{k}_i{self.me}", s.nData * s.row_bytes, zero=False)
                            for k, s in enumerate(specs)]
         self.tables_buf = self.heap.alloc("tables", self.P * 2 * self.n_max * 8)
-        self.flags_buf = self.heap.alloc("flags", 4096)
+        self.flags_buf = self.heap.alloc("flags", N.FLAG_PAGE_BYTES)
         ring_row = max(s.dst_row_bytes for s in specs)
         self.ring_depth = config.ring_depth
         self.ring_buf = self.heap.alloc("ring", self.ring_depth * self.B * ring_row, zero=False)
@@ -321,11 +321,14 @@ class DeviceEngine:
                 views = [self.heap.peer_buffer(where(g // self.P), f"shard{g % self.P}_i{g // self.P}").numpy(
                     np.uint8, (specs[g % self.P].nData, specs[g % self.P].row_bytes)) for g in range(n_sources)]
                 self.plans.append(CpuGather(views, s))
+        self._status = None
+        self._perm_scratch = None
         self.push = config.exchange == "push" and self.cuda and not self.host_resident
         if self.push:
             self.init_push()
         self._barrier_epoch = 0
         self._barrier_tensor = None
+        self._distinct_gpus = None
         self._flag_pages = None
         self._closed = False
 
@@ -401,8 +404,9 @@ class DeviceEngine:
         if not self.cuda:
             self.plans[k].lengths = self.lens_all.numpy()
             return
-        if self.stage is not None or self.push:
-            raise NotImplementedError("variable-size windows use the HBM/zero-copy pull path")
+        if self.stage is not None:
+            raise NotImplementedError("variable-size windows use the kernel paths (HBM or host_stage='pull'), "
+                                      "not the memcpy/gather staging")
         es = s.np_dtype.itemsize
         self.lens_all_dev = self.lens_all.to(self.device)                           # elements
         self._lens_dev = (self.lens_all * es).to(self.device)                       # payload bytes
@@ -428,12 +432,17 @@ class DeviceEngine:
                 self.states[k].copy_(torch.from_numpy(rng.to_words()))
 
     def stream_barrier(self) -> None:
-        """All consumers' side streams meet here (orders table reads/writes across GPUs)."""
+        """All consumers' side streams meet here (orders table reads/writes across GPUs).
+
+        Default on GPUs: the flag-barrier kernel (csrc/flags.cu) -- peer stores into every rank's
+        flag page + a bounded acquire-poll, no library collective on the shuffle path.  It needs one
+        GPU per rank (kernels of several ranks on one GPU must not wait on one another); ranks that
+        share a GPU, and CPU runs, meet on the host instead."""
         if self.n_instances == 1:
             return
         mode = self.cfg.barrier
         if mode == "auto":
-            mode = "nccl" if self.cuda and _nccl_ready() else "host"
+            mode = "flags" if self.cuda and self._one_gpu_per_rank() else "host"
         if mode == "nccl":
             import torch.distributed as dist
 
@@ -447,15 +456,63 @@ class DeviceEngine:
             self.side.synchronize()
             self.comm.barrier()
 
+    def _one_gpu_per_rank(self) -> bool:
+        if self._distinct_gpus is None:
+            import os
+
+            props = torch.cuda.get_device_properties(self.device)
+            gpu = str(getattr(props, "uuid", "")) or f"{os.getpid()}:{self.device.index}"
+            ids = self.comm.allgather_obj((os.uname().nodename, gpu))
+            self._distinct_gpus = len({str(i) for i in ids}) == len(ids)
+        return self._distinct_gpus
+
+    def _status_word(self):
+        """Mapped host word that bounded device-side waits write when they give up (1 timed out,
+        2 stopped); read by the host without synchronising."""
+        if self._status is None:
+            self._status_buf, self._status_dev = self.heap.alloc_pinned("wait_status", 64)
+            self._status = self._status_buf.numpy(np.uint32, (16,))
+            self._status[:] = 0
+        return self._status
+
+    def check_waits(self) -> None:
+        if self._status is not None and self._status[0]:
+            from .exceptions import LoaderTimeoutError
+
+            code = int(self._status[0])
+            what = {1: "timed out", 2: "was stopped"}.get(code & 15, "failed")
+            which = {0: "a peer's flag", 1: f"the `free` word of consumer {code >> 8}",
+                     2: f"the `table` word of consumer {code >> 8}", 3: "this rank's `ready` word"}.get((code >> 4) & 15)
+            raise LoaderTimeoutError(f"a bounded device-side wait on {which} {what} (timeout_s={self.cfg.timeout_s}); "
+                                     f"flag page: {self.flag_page_summary()}")
+
+    def flag_page_summary(self) -> str:
+        """This rank's counters, copied out on a private stream (diagnostics after a failed wait)."""
+        try:
+            st = torch.cuda.Stream(self.device)
+            with torch.cuda.stream(st):
+                w = self.flags_buf.tensor(torch.int32, (N.FLAG_PAGE_BYTES // 4,)).to("cpu", non_blocking=True)
+            st.synchronize()
+            R, D = self.n_instances, self.ring_depth
+            M = N.FLAG_MAX_RANKS
+            return str({"ready": w[N.FLAG_READY0:N.FLAG_READY0 + D].tolist(),
+                        "free": [w[N.FLAG_FREE0 + s * M:N.FLAG_FREE0 + s * M + R].tolist() for s in range(D)],
+                        "done": [w[N.FLAG_DONE0 + s * M:N.FLAG_DONE0 + s * M + R].tolist() for s in range(D)],
+                        "table": [w[N.FLAG_TABLE0 + k * M:N.FLAG_TABLE0 + k * M + R].tolist() for k in range(self.P)],
+                        "use": getattr(self, "_use", None)})
+        except Exception as e:  # diagnostics must never mask the timeout itself
+            return f"unavailable ({e})"
+
     def _flag_barrier(self) -> None:
         if self._flag_pages is None:
             pages = [self.heap.peer_ptr(r, "flags") for r in range(self.n_instances)]
             self._flag_pages = torch.tensor(pages, dtype=torch.int64).to(self.device)
-            self._flag_status = torch.zeros(1, dtype=torch.int32, device=self.device)
+            self._status_word()
+        self.check_waits()
         self._barrier_epoch += 1
         polls = int(self.cfg.timeout_s * 2e6)
         N.check(N.lib().bddl_flag_barrier(self._flag_pages.data_ptr(), self.n_instances, self.me,
-                                          self._barrier_epoch, polls, None, self._flag_status.data_ptr(),
+                                          self._barrier_epoch, polls, None, C.c_void_p(self._status_dev),
                                           C.c_void_p(self.side.cuda_stream)))
         self.launches += 1
 
@@ -494,8 +551,11 @@ class DeviceEngine:
         tbl = self.tables[k, self.cur[k]].unsqueeze(0)
         st = self.states[k].unsqueeze(0)
         if self.cuda:
+            if self._perm_scratch is None:  # one scratch for all windows: they shuffle in turn on the side stream
+                self._perm_scratch = torch.empty(int(N.lib().bddl_perm_gen_scratch_bytes(self.n_max)) + 64,
+                                                 dtype=torch.uint8, device=self.device)
             with torch.cuda.stream(self.side):
-                T.perm_gen(tbl, st, n=n, stream=self.side)
+                T.perm_gen(tbl, st, n=n, stream=self.side, scratch=self._perm_scratch)
             self.launches += 1
         else:
             T.perm_gen(tbl, st, n=n)
@@ -554,60 +614,60 @@ class DeviceEngine:
             slots = self.tables[k, buf, first_row:first_row + n].numpy()
             self.plans[k].run(slots, self.ring[ring_slot])
 
-    # -- push form of the exchange (owner-side stores over NVLink + flags) ---------------------------------
-    # Every rank scans every consumer's batch slice, delivers the samples it owns into that
-    # consumer's ring slot with peer stores, and bumps the consumer's `ready` counter
-    # (red.release.sys).  Consumers wait on their own counter with cuStreamWaitValue32 and hand a
-    # slot back by storing its use count into every owner's `free` word (st.release.sys) -- the
-    # reference's lend/return tokens (ddl/connection.py:153-182) as NVLink-visible counters.
-    _READY0, _FREE0 = 64, 128
-
+    # -- push form of the exchange (owner-side stores over NVLink + in-kernel flags) ---------------------
+    # One launch per step and GPU (csrc/gather.cu, push_tma_cvt_kernel): every rank scans every
+    # consumer's batch slice, delivers the samples it owns into that consumer's ring slot with
+    # stores over NVLink and bumps the consumer's `ready` word from inside the kernel
+    # (red.release.sys); the same kernel first waits for the consumer's `free` and `table` words and
+    # finally for its own `ready` word -- the reference's lend/return tokens
+    # (ddl/connection.py:153-182) as NVLink-visible counters, all waits bounded.
     def init_push(self) -> None:
         R, D = self.n_instances, self.ring_depth
-        if R * 16 + self._FREE0 > 1024 or D > 16:
-            raise ValueError("push exchange supports up to 56 instances and ring_depth <= 16")
+        if R > N.FLAG_MAX_RANKS or D > N.FLAG_MAX_SLOTS or self.P > N.FLAG_MAX_WINDOWS:
+            raise ValueError(f"push exchange supports up to {N.FLAG_MAX_RANKS} instances, ring_depth <= "
+                             f"{N.FLAG_MAX_SLOTS} and {N.FLAG_MAX_WINDOWS} producers per instance")
+        if self.remote_storage:
+            raise NotImplementedError("the push form needs the shards on the consumer GPUs (no storage ranks)")
         self._use = [0] * D
-        self._wait_status = torch.zeros(1, dtype=torch.int32, device=self.device)
-        ready = [[self.heap.peer_ptr(c, "flags") + 4 * (self._READY0 + s) for s in range(D)] for c in range(R)]
-        free = [[self.heap.peer_ptr(o, "flags") + 4 * (self._FREE0 + self.me * 16 + s) for o in range(R)]
-                for s in range(D)]
-        self._ready_targets = torch.tensor(ready, dtype=torch.int64).to(self.device)   # [R, D]
-        self._free_targets = torch.tensor(free, dtype=torch.int64).to(self.device)     # [D, R]
-        self.push_plans = []
-        for s in self.specs:
-            plan = GatherPlan(self.sources, s.row_bytes, s.sample_bytes, s.convert, dst_row_bytes=self.ring_row,
-                              variant=self.cfg.gather_variant, max_ctas=self.cfg.gather_max_ctas,
-                              tune=self.cfg.gather_tune, col_offset_bytes=s.col_off)
-            plan.set_filter(self.me * self.P, (self.me + 1) * self.P)
-            self.push_plans.append(plan)
+        flag_pages = [self.heap.peer_ptr(r, "flags") for r in range(R)]
+        dev = lambda xs: torch.tensor(xs, dtype=torch.int64).to(self.device)  # noqa: E731
+        self._push_tables = dev([self.heap.peer_ptr(r, "tables") for r in range(R)])
+        self._push_rings = dev([self.heap.peer_ptr(r, "ring") for r in range(R)])
+        self._push_flags = dev(flag_pages)
+        # consumer -> owners: "I consumed fill number `use` of my ring slot"
+        self._free_targets = dev([[p + 4 * (N.FLAG_FREE0 + s * N.FLAG_MAX_RANKS + self.me) for p in flag_pages]
+                                  for s in range(D)])                           # [D, R]
+        # consumer -> owners: "my slot table number `seq` of window k is complete"
+        self._table_targets = dev([[p + 4 * (N.FLAG_TABLE0 + k * N.FLAG_MAX_RANKS + self.me) for p in flag_pages]
+                                   for k in range(self.P)])                     # [P, R]
+        self._status_word()  # bounded waits report here
+        g = C.c_int32()
+        N.check(N.lib().bddl_push_ctas_per_consumer(R, self.cfg.gather_max_ctas, C.byref(g)))
+        d = N.PushDesc()
+        d.d_tables, d.d_rings, d.d_flags = (self._push_tables.data_ptr(), self._push_rings.data_ptr(),
+                                            self._push_flags.data_ptr())
+        d.d_status = self._status_dev
+        d.max_polls = int(self.cfg.timeout_s * 2e6)
+        d.n_ranks, d.me, d.ctas_per_consumer = R, self.me, g.value
+        d.owner_lo, d.owner_hi = self.me * self.P, (self.me + 1) * self.P
+        self._push_desc = d
 
-    def _wait_flag(self, sp, addr: int, value: int) -> None:
-        lib = N.lib()
-        if self.cfg.push_wait == "stream":
-            N.check(lib.bddl_stream_wait_value32(sp, C.c_void_p(addr), value))
-        else:
-            N.check(lib.bddl_flag_wait(C.c_void_p(addr), value, int(self.cfg.timeout_s * 2e6), None,
-                                       C.c_void_p(self._wait_status.data_ptr()), sp))
-            self.launches += 1
+    def signal_table_ready(self, k: int, seq: int) -> None:
+        """Side stream, after window k's table number ``seq`` was produced: tell every owner."""
+        N.check(N.lib().bddl_flag_signal(C.c_void_p(self._table_targets[k].data_ptr()), self.n_instances, seq, 0,
+                                         C.c_void_p(self.side.cuda_stream)))
+        self.launches += 1
 
-    def push_step(self, k: int, buf: int, first_row: int, ring_slot: int, stream) -> None:
-        lib, R, n = N.lib(), self.n_instances, self.B
-        sp = C.c_void_p(stream.cuda_stream)
-        use = self._use[ring_slot]
-        flags = self.flags_buf.ptr
-        table_off = ((k * 2 + buf) * self.n_max + first_row) * 8
-        ring_off = ring_slot * self.B * self.ring_row
-        for i in range(R):
-            c = (self.me + i) % R  # staggered so that owners do not all hit one consumer at once
-            if use > 0:  # consumer c must have released the slot's previous contents
-                self._wait_flag(sp, flags + 4 * (self._FREE0 + c * 16 + ring_slot), use)
-            self.push_plans[k].run_ptr(self.heap.peer_ptr(c, "tables") + table_off,
-                                       self.heap.peer_ptr(c, "ring") + ring_off, n, stream.cuda_stream)
-            N.check(lib.bddl_flag_signal(C.c_void_p(self._ready_targets[c, ring_slot:].data_ptr()), 1, 1, 1, sp))
-            self.launches += 2
-        self._use[ring_slot] = use + 1
-        # ... and as a consumer: all R owners have delivered their share of my batch
-        self._wait_flag(sp, flags + 4 * (self._READY0 + ring_slot), R * (use + 1))
+    def push_step(self, k: int, buf: int, first_row: int, ring_slot: int, stream, table_seq: int) -> None:
+        self.check_waits()
+        d = self._push_desc
+        d.table_offset_bytes = ((k * 2 + buf) * self.n_max + first_row) * 8
+        d.ring_offset_bytes = ring_slot * self.B * self.ring_row
+        d.ring_slot, d.window = ring_slot, k
+        d.use, d.table_seq = self._use[ring_slot], table_seq
+        self.plans[k].push_ptr(d, self.B, stream.cuda_stream)
+        self._use[ring_slot] += 1
+        self.launches += 1
 
     def release_slot(self, ring_slot: int, stream) -> None:
         """Consumer side of the push form: tell every owner that `ring_slot` may be refilled."""

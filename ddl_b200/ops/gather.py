@@ -167,9 +167,14 @@ class GatherPlan:
         self._fn = N.lib().bddl_exchange_gather_collate
         self._step = N.lib().bddl_gather_step
 
-    def set_filter(self, lo: int, hi: int) -> None:
-        """Push form: deliver only slots whose source id is in [lo, hi) (0, 0 = everything)."""
-        self._desc.filter_lo, self._desc.filter_hi = int(lo), int(hi)
+    def push_ptr(self, push_desc, n_samples: int, stream_ptr: int) -> None:
+        """Push form (``bddl_exchange_push_collate``): this GPU delivers the samples it owns into
+        every consumer's ring slot; ``push_desc`` is a filled ``_native.PushDesc``."""
+        d = self._desc
+        d.d_slots, d.d_dst, d.n_samples = None, None, n_samples
+        rc = N.lib().bddl_exchange_push_collate(C.byref(d), C.byref(push_desc), C.c_void_p(stream_ptr))
+        if rc:
+            N.check(rc)
 
     def alloc_batch(self, n_samples: int) -> torch.Tensor:
         """Raw batch buffer [n_samples, dst_row_bytes] uint8 (rows 16-byte aligned)."""

@@ -52,7 +52,22 @@ def slot_iota(table: torch.Tensor, source: int, first_row: int = 0, stream=None)
                     + (int(source) << N.SLOT_ROW_BITS))
 
 
-def perm_gen(tables: torch.Tensor, states: torch.Tensor, n: Optional[int] = None, stream=None) -> None:
+_perm_scratch: dict = {}
+
+
+def perm_gen_scratch(device: torch.device, n: int, n_tables: int = 1) -> torch.Tensor:
+    """Device scratch for ``perm_gen`` (targets, reservation words, work lists: 20 bytes per entry),
+    cached per device and grown on demand so the shuffle path never allocates in steady state."""
+    need = n_tables * ((int(N.lib().bddl_perm_gen_scratch_bytes(n)) + 63) // 64 * 64)
+    key = (device.type, device.index)
+    buf = _perm_scratch.get(key)
+    if buf is None or buf.numel() < need:
+        buf = _perm_scratch[key] = torch.empty(need, dtype=torch.uint8, device=device)
+    return buf
+
+
+def perm_gen(tables: torch.Tensor, states: torch.Tensor, n: Optional[int] = None, stream=None,
+             scratch: Optional[torch.Tensor] = None) -> None:
     """Shuffle each row of ``tables`` ([T, stride] int64) in place with ``states`` ([T, 6] int64).
 
     Device tensors run the sm_100a kernel; CPU tensors run the host Fisher-Yates.  Both advance
@@ -69,8 +84,10 @@ def perm_gen(tables: torch.Tensor, states: torch.Tensor, n: Optional[int] = None
     if tables.stride(1) != 1 or not states.is_contiguous():
         raise ValueError("perm_gen needs unit-stride tables and contiguous states")
     if tables.is_cuda:
+        if scratch is None:
+            scratch = perm_gen_scratch(tables.device, n, T)
         N.check(N.lib().bddl_perm_gen(tables.data_ptr(), tables.stride(0), n, states.data_ptr(), T,
-                                      _stream_ptr(tables.device, stream)))
+                                      scratch.data_ptr(), scratch.numel(), _stream_ptr(tables.device, stream)))
         return
     for t in range(T):
         r = Pcg64(0)

@@ -18,7 +18,7 @@
 extern "C" {
 #endif
 
-#define BDDL_ABI_VERSION 1
+#define BDDL_ABI_VERSION 2
 
 #define BDDL_ERR_INVALID (-1)
 #define BDDL_ERR_UNSUPPORTED (-2)
@@ -61,9 +61,13 @@ int bddl_partner_select(bddl_rng_state* s, int32_t n_instance, int32_t my_rank, 
 /* ---- N2: perm_gen (replaces the in-place row shuffle rng.shuffle(my_ary), invoked at
  *      ddl/datapusher.py:154).  Shuffles n_tables slot tables of n entries each (table t starts
  *      at d_tables + t*table_stride) with the RNG states d_states[t], which are advanced in
- *      place on the device.  Bit-exact with bddl_host_shuffle_u64.  One warp per table. ----- */
+ *      place on the device.  Bit-exact with bddl_host_shuffle_u64.  One CTA of 1024 threads per
+ *      table: block-parallel draw generation and accept/reject, then the swaps applied in
+ *      O(log n) rounds of deterministic reservations.  d_scratch: caller-owned device memory,
+ *      n_tables * round_up(bddl_perm_gen_scratch_bytes(n), 64) bytes, 16-byte aligned. -------- */
+int64_t bddl_perm_gen_scratch_bytes(int64_t n);
 int bddl_perm_gen(uint64_t* d_tables, int64_t table_stride, int64_t n, bddl_rng_state* d_states,
-                  int32_t n_tables, void* stream);
+                  int32_t n_tables, void* d_scratch, int64_t scratch_bytes, void* stream);
 
 /* ---- N4: index_exchange (replaces the two Sendrecv_replace calls of
  *      SendRecvReplaceGlobalShuffler.global_shuffle, ddl/shuffle.py:92-108) on slot tables:
@@ -110,8 +114,8 @@ typedef struct bddl_gather_desc {
     uint32_t pad_bits;               /* variable-size: output element used for padding            */
     int32_t variant;                 /* BDDL_VARIANT_*                                            */
     int32_t max_ctas;                /* SM budget; 0 = one CTA per SM                             */
-    int32_t filter_lo;               /* push form: only slots whose source is in [filter_lo,         */
-    int32_t filter_hi;               /* filter_hi) are delivered (0,0 = deliver everything)          */
+    int32_t reserved0;               /* (was the source filter of the two-launch push form)          */
+    int32_t reserved1;
     int32_t col_offset_bytes;        /* deliver sample bytes [col_offset, col_offset + sample_bytes) (multiple of 16) */
     int32_t tune;                    /* stage ring per warp; convert: 0 = 16 warps x 3 x 4 KiB, 1 = 16 x 6 x 2 KiB, 2 = 8 x 3 x 8 KiB, 3 = 32 x 3 x 2 KiB */
 } bddl_gather_desc;
@@ -119,6 +123,45 @@ typedef struct bddl_gather_desc {
 int bddl_exchange_gather_collate(const bddl_gather_desc* desc, void* stream);
 /* One loader step in one call: [cudaStreamWaitEvent(wait_event)] -> assemble -> [cudaEventRecord(record_event)]. */
 int bddl_gather_step(const bddl_gather_desc* desc, void* stream, void* wait_event, void* record_event);
+
+/* Push form of N5 (the "DataPusher" direction, ddl/datapusher.py:147-170, with the lend/return
+ * tokens of ddl/connection.py:153-182 written from inside the kernel).  One launch per loader
+ * step on every GPU: each GPU scans every consumer's slice of its slot table, delivers the samples
+ * it owns into that consumer's ring slot with stores over NVLink, and the last CTA working for a
+ * consumer adds 1 to that consumer's `ready` word (red.release.sys).  The kernel first waits,
+ * bounded, for the consumer's `free` word of the ring slot and for its `table` word; CTA 0 finally
+ * waits, bounded, until all n_ranks owners have bumped this GPU's own `ready` word, so the kernel's
+ * completion means "my batch is assembled".  *d_status (device or mapped host memory) receives
+ * 1 (timed out) or 2 (stopped) when a wait gives up.  `desc` is a gather descriptor whose d_slots and
+ * d_dst are ignored.  Flag page layout (32-bit words, one page of BDDL_FLAG_PAGE_BYTES per rank): */
+#define BDDL_FLAG_PAGE_BYTES 16384
+#define BDDL_FLAG_MAX_RANKS 64
+#define BDDL_FLAG_MAX_SLOTS 16
+#define BDDL_FLAG_MAX_WINDOWS 24
+#define BDDL_FLAG_BARRIER0 0      /* [rank]              flag barrier slots                          */
+#define BDDL_FLAG_READY0 256      /* [slot]              += 1 by every owner per fill of my slot     */
+#define BDDL_FLAG_STOP 272        /*                     non-zero cancels every wait                 */
+#define BDDL_FLAG_FREE0 512       /* [slot][consumer]    = fills consumed, stored by that consumer   */
+#define BDDL_FLAG_DONE0 1536      /* [slot][consumer]    local CTA tickets of the push kernel        */
+#define BDDL_FLAG_TABLE0 2560     /* [window][consumer]  = tables produced, stored by that consumer  */
+typedef struct bddl_push_desc {
+    const void* const* d_tables;  /* device array [n_ranks]: every consumer's slot-table buffer      */
+    void* const* d_rings;         /* device array [n_ranks]: every consumer's batch ring             */
+    uint32_t* const* d_flags;     /* device array [n_ranks]: every rank's flag page                  */
+    int64_t table_offset_bytes;   /* where this step's slice starts inside a table buffer            */
+    int64_t ring_offset_bytes;    /* where the ring slot starts inside a ring                        */
+    uint64_t max_polls;           /* bound of every in-kernel wait (0 = unbounded)                   */
+    uint32_t* d_status;
+    int32_t n_ranks, me;
+    int32_t ring_slot, window;
+    int32_t owner_lo, owner_hi;   /* source ids [lo, hi) whose shards live on this GPU               */
+    int32_t ctas_per_consumer;    /* from bddl_push_ctas_per_consumer; the same on every launch      */
+    uint32_t use;                 /* how often this ring slot has been filled before                 */
+    uint32_t table_seq;           /* the consumers' `table` words must have reached this value       */
+} bddl_push_desc;
+int bddl_push_ctas_per_consumer(int32_t n_ranks, int32_t max_ctas, int32_t* out);
+int bddl_exchange_push_collate(const bddl_gather_desc* desc, const bddl_push_desc* push, void* stream);
+
 /* Number of kernels this library has launched in this process (for gpu_launches accounting). */
 int64_t bddl_launch_count(void);
 

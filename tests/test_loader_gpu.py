@@ -200,36 +200,54 @@ def test_process_transport_converts_on_the_gpu(tmp_path, host_pull):
     assert np.array_equal(np.load(os.path.join(str(tmp_path), "seen_0.npy")), exp)
 
 
-@pytest.mark.multigpu
-def test_two_gpus_push_exchange(tmp_path):
-    """Push form: every GPU stores the samples it owns into its peer's batch ring over NVLink."""
-    cfg = {"n_instances": 2, "n_producers": 1, "n": 4096, "v": 32, "B": 256, "epochs": 5, "fraction": 0.5,
-           "shuffle_mode": "device", "declare_seed": True, "cpu": False}
-    os.environ["DDL_B200_EXCHANGE"] = "push"
-    try:
-        _torchrun(2, cfg, tmp_path)
-    finally:
-        os.environ.pop("DDL_B200_EXCHANGE", None)
-    exp = expected_epochs(2, 1, 4096, 256, 5, 0.5)
-    for i in range(2):
-        assert np.array_equal(np.load(os.path.join(str(tmp_path), f"seen_{i}.npy")), exp[i])
+def _need_gpus(n):
+    if torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} CUDA devices")
+
+
+def _check_order(tmp_path, n_inst, P, n, B, E, fraction):
+    exp = expected_epochs(n_inst, P, n, B, E, fraction)
+    for i in range(n_inst):
+        assert np.array_equal(np.load(os.path.join(str(tmp_path), f"seen_{i}.npy")), exp[i]), f"instance {i}"
 
 
 @pytest.mark.multigpu
-@pytest.mark.parametrize("barrier", ["nccl", "flags", "host"])
-def test_two_gpus_global_shuffle_over_nvlink(tmp_path, barrier):
+@pytest.mark.parametrize("nproc", [2, 4, 8])
+def test_multi_gpu_push_exchange(tmp_path, nproc):
+    """Push form, one launch per step and GPU: every GPU stores the samples it owns into its peers'
+    batch rings over NVLink and signals `ready` from inside the kernel; order equals the oracle
+    (partner tables with real 3-cycles from 3 instances on, reference ddl/shuffle.py:50-79)."""
+    _need_gpus(nproc)
+    cfg = {"n_instances": nproc, "n_producers": 2, "n": 4096, "v": 32, "B": 256, "epochs": 6, "fraction": 0.5,
+           "shuffle_mode": "device", "declare_seed": True, "cpu": False, "exchange": "push", "timeout_s": 60.0,
+           "ring_depth": 4, "prefetch_depth": 2, "fetch_streams": 2}
+    _torchrun(nproc, cfg, tmp_path)
+    _check_order(tmp_path, nproc, 2, 4096, 256, 6, 0.5)
+
+
+@pytest.mark.multigpu
+@pytest.mark.parametrize("nproc,barrier", [(2, "nccl"), (2, "flags"), (2, "host"), (4, "flags"), (8, "flags"),
+                                           (8, "nccl")])
+def test_multi_gpu_global_shuffle_over_nvlink(tmp_path, nproc, barrier):
     """One process per GPU: slot tables exchanged and samples pulled through peer mappings."""
-    cfg = {"n_instances": 2, "n_producers": 2, "n": 4096, "v": 32, "B": 256, "epochs": 6, "fraction": 0.5,
-           "shuffle_mode": "device", "declare_seed": True, "cpu": False}
-    env_extra = {"DDL_B200_BARRIER": barrier}
-    os.environ.update(env_extra)
-    try:
-        _torchrun(2, cfg, tmp_path)
-    finally:
-        os.environ.pop("DDL_B200_BARRIER", None)
-    exp = expected_epochs(2, 2, 4096, 256, 6, 0.5)
-    for i in range(2):
-        assert np.array_equal(np.load(os.path.join(str(tmp_path), f"seen_{i}.npy")), exp[i])
+    _need_gpus(nproc)
+    cfg = {"n_instances": nproc, "n_producers": 2, "n": 4096, "v": 32, "B": 256, "epochs": 6, "fraction": 0.5,
+           "shuffle_mode": "device", "declare_seed": True, "cpu": False, "barrier": barrier, "timeout_s": 60.0}
+    _torchrun(nproc, cfg, tmp_path)
+    _check_order(tmp_path, nproc, 2, 4096, 256, 6, 0.5)
+
+
+@pytest.mark.multigpu
+@pytest.mark.parametrize("nproc,exchange", [(2, "pull"), (8, "pull"), (2, "push"), (8, "push")])
+def test_multi_gpu_u8_to_bf16_with_integrity_mode(tmp_path, nproc, exchange):
+    """uint8 rows of 4 KiB through the TMA/convert form across GPUs: ids and payloads must match,
+    and (pull) every batch is re-assembled by the LDG form and fingerprinted (verify=True)."""
+    _need_gpus(nproc)
+    cfg = {"n_instances": nproc, "n_producers": 1, "n": 2048, "v": 4096, "B": 128, "epochs": 4, "fraction": 0.5,
+           "shuffle_mode": "device", "cpu": False, "u8": True, "verify": exchange == "pull", "exchange": exchange,
+           "ring_depth": 3, "prefetch_depth": 2, "timeout_s": 60.0}
+    _torchrun(nproc, cfg, tmp_path)
+    _check_order(tmp_path, nproc, 1, 2048, 128, 4, 0.5)
 
 
 @pytest.mark.multigpu

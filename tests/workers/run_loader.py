@@ -14,6 +14,29 @@ import ddl_b200 as ddl  # noqa: E402
 CFG = json.loads(os.environ["BDDL_TEST_CFG"])
 
 
+class ByteProducer(ddl.ProducerFunctionSkeleton):
+    """uint8 rows: bytes 0..3 = global id (little endian), the rest a pattern derived from it;
+    delivered as bf16 through the fused convert (scale 1, bias 0: every byte value is exact)."""
+
+    def __init__(self, n, v):
+        super().__init__()
+        self.n, self.v = n, v
+
+    def on_init(self, **kw):
+        super().on_init(**kw)
+        from ddl_b200 import _native as N
+
+        cv = ddl.Convert(N.CVT_U8_BF16, (1.0,), (0.0,), 0)
+        return ddl.DataProducerOnInitReturn(self.n, self.v, (self.n, self.v), (4, self.v - 4), dtype=np.uint8,
+                                            convert=cv, shuffle_seed=self.rank_global)
+
+    def post_init(self, **kw):
+        a = kw["my_ary"]
+        gid = (self.rank_global * 1_000_000 + np.arange(self.n)).astype(np.int64)
+        a[:, :4] = gid.astype("<u4").view(np.uint8).reshape(self.n, 4)
+        a[:, 4:] = ((gid[:, None] * 7 + np.arange(self.v - 4)[None, :]) % 251).astype(np.uint8)
+
+
 class IdProducer(ddl.ProducerFunctionSkeleton):
     def __init__(self, n, v, declare_seed, group_size):
         super().__init__()
@@ -46,8 +69,9 @@ class IdProducer(ddl.ProducerFunctionSkeleton):
 def body(env, conn):
     n, v, B, E = CFG["n"], CFG["v"], CFG["B"], CFG["epochs"]
     group_size = env.n_producers + 1
-    loader = ddl.DistributedDataLoader(IdProducer(n, v, CFG.get("declare_seed", False), group_size), B, conn, E,
-                                       CFG.get("fraction", 0.0), "sendrecv_replace", env.color, env.n_instances)
+    producer = ByteProducer(n, v) if CFG.get("u8") else IdProducer(n, v, CFG.get("declare_seed", False), group_size)
+    loader = ddl.DistributedDataLoader(producer, B, conn, E, CFG.get("fraction", 0.0), "sendrecv_replace", env.color,
+                                       env.n_instances)
     seen = []
     if CFG.get("die_after"):
         try:
@@ -60,6 +84,21 @@ def body(env, conn):
                 fh.write(str(err))
             os._exit(0)
         os._exit(3)
+    if CFG.get("u8"):
+        pat = torch.arange(v - 4, device=env.device)[None, :]
+        w = torch.tensor([1, 256, 65536, 16777216], device=env.device)
+        for e in range(E):
+            ids = []
+            for a, b in loader:
+                assert a.dtype == torch.bfloat16 and a.shape == (B, 4) and b.shape == (B, v - 4)
+                gid = (a.long() * w).sum(dim=1)
+                assert torch.equal(b.long(), (gid[:, None] * 7 + pat) % 251), "payload does not belong to its id"
+                ids.append(gid.cpu().numpy())
+                loader.mark(ddl.Marker.END_OF_BATCH)
+            loader.mark(ddl.Marker.END_OF_EPOCH)
+            seen.append(np.concatenate(ids))
+        np.save(os.path.join(CFG["out"], f"seen_{env.color}.npy"), np.stack(seen))
+        return
     if CFG.get("defer"):
         # no host synchronisation per batch: the fetch streams are held back on the device while the
         # host races ahead through window hand-overs; batches are only looked at after the last epoch
@@ -96,7 +135,10 @@ def body(env, conn):
 
 if __name__ == "__main__":
     cfg = ddl.LoaderConfig.from_env(compat=CFG.get("compat"), shuffle_mode=CFG.get("shuffle_mode"),
-                                    timeout_s=CFG.get("timeout_s", 120.0))
+                                    timeout_s=CFG.get("timeout_s", 120.0), verify=CFG.get("verify"),
+                                    exchange=CFG.get("exchange"), barrier=CFG.get("barrier"),
+                                    ring_depth=CFG.get("ring_depth"), prefetch_depth=CFG.get("prefetch_depth"),
+                                    fetch_streams=CFG.get("fetch_streams"))
     main = ddl.distributed_dataloader(body, n_instances=CFG["n_instances"], n_producers=CFG.get("n_producers"),
                                       config=cfg, device="cpu" if CFG.get("cpu", True) else None,
                                       n_storage=CFG.get("n_storage", 0))
