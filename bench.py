@@ -89,7 +89,7 @@ def run_ours(args) -> dict:
     cfg = ddl.LoaderConfig.from_env(metrics=False, ring_depth=args.ring, gather_variant=args.variant,
                                     gather_tune=args.tune, prefetch_depth=args.prefetch_depth,
                                     fetch_streams=args.fetch_streams, exchange=args.exchange,
-                                    gather_max_ctas=args.max_ctas)
+                                    gather_max_ctas=args.max_ctas, timeout_s=args.timeout_s)
     if not args.e2e_only:
         ddl.distributed_dataloader(body, n_instances="world", n_producers=1, config=cfg)()
 
@@ -203,9 +203,15 @@ def main():
     ap.add_argument("--e2e-tune", type=int, default=0)
     ap.add_argument("--host-threads", type=int, default=4)
     ap.add_argument("--host-stage", default="pull", choices=["gather", "memcpy", "pull"])
+    ap.add_argument("--timeout-s", type=float, default=None, help="bound of every device/host wait of the loader")
+    ap.add_argument("--watchdog", type=float, default=0.0, help="dump all Python stacks to stderr after this many seconds")
     ap.add_argument("--min-seconds", type=float, default=1.0, help="minimum length of the device-timed region")
     ap.add_argument("--e2e-min-seconds", type=float, default=0.5, help="minimum length of the e2e timed region")
     args = ap.parse_args()
+    if args.watchdog > 0:
+        import faulthandler
+
+        faulthandler.dump_traceback_later(args.watchdog, exit=False, file=sys.stderr)
     if args.warmup < 3:
         args.warmup = 3
     if args.impl == "reference":

@@ -47,28 +47,16 @@ __global__ void flag_signal_kernel(uint32_t* const* targets, int n, uint32_t val
 }
 
 // status: 0 = satisfied, 1 = timed out, 2 = stopped.
-__global__ void flag_wait_kernel(const uint32_t* flag, uint32_t value, unsigned long long max_polls,
+__global__ void flag_wait_kernel(const uint32_t* flag, uint32_t value, unsigned long long timeout_ns,
                                  const uint32_t* stop, uint32_t* status) {
-    unsigned long long polls = 0;
-    uint32_t st = 0;
-    while ((int32_t)(ld_acquire_sys_u32(flag) - value) < 0) {
-        if (stop && ld_acquire_sys_u32(stop) != 0) {
-            st = 2;
-            break;
-        }
-        if (++polls >= max_polls) {
-            st = 1;
-            break;
-        }
-        __nanosleep(200);
-    }
-    if (status) *status = st;
+    const uint32_t st = poll_geq(flag, value, stop, timeout_ns);
+    if (status) st_release_sys_u32(status, st);
 }
 
 // All-ranks barrier on the flag page: rank `me` writes `epoch` into slot `me` of every rank's
 // page (peer stores), then waits until every slot of its own page has reached `epoch`.
 __global__ void flag_barrier_kernel(uint32_t* const* pages, int n_ranks, int me, uint32_t epoch,
-                                    unsigned long long max_polls, const uint32_t* stop, uint32_t* status) {
+                                    unsigned long long timeout_ns, const uint32_t* stop, uint32_t* status) {
     const int t = threadIdx.x;
     if (t < n_ranks) {
         fence_sys();
@@ -76,22 +64,8 @@ __global__ void flag_barrier_kernel(uint32_t* const* pages, int n_ranks, int me,
     }
     __syncthreads();
     uint32_t st = 0;
-    if (t < n_ranks) {
-        const uint32_t* mine = pages[me] + t;
-        unsigned long long polls = 0;
-        while ((int32_t)(ld_acquire_sys_u32(mine) - epoch) < 0) {
-            if (stop && ld_acquire_sys_u32(stop) != 0) {
-                st = 2;
-                break;
-            }
-            if (++polls >= max_polls) {
-                st = 1;
-                break;
-            }
-            __nanosleep(200);
-        }
-    }
-    if (st && status) st_release_sys_u32(status, st);  // may be mapped host memory: no atomics
+    if (t < n_ranks) st = poll_geq(pages[me] + t, epoch, stop, timeout_ns);
+    if (st && status) st_release_sys_u32(status, st | ((uint32_t)t << 8));  // may be mapped host memory: no atomics
 }
 
 }  // namespace
@@ -128,23 +102,22 @@ int bddl_flag_signal(uint32_t* const* d_targets, int32_t n, uint32_t value, int3
     return 0;
 }
 
-int bddl_flag_wait(const uint32_t* d_flag, uint32_t value, uint64_t max_polls, const uint32_t* d_stop,
+int bddl_flag_wait(const uint32_t* d_flag, uint32_t value, uint64_t timeout_ns, const uint32_t* d_stop,
                    uint32_t* d_status, void* stream) {
     if (!d_flag) return bddl_fail(BDDL_ERR_INVALID, "flag_wait: null flag");
-    flag_wait_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(d_flag, value, max_polls ? max_polls : ~0ULL, d_stop,
-                                                         d_status);
+    flag_wait_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(d_flag, value, timeout_ns, d_stop, d_status);
     bddl_count_launch(1);
     BDDL_CUDA(cudaGetLastError());
     return 0;
 }
 
-int bddl_flag_barrier(uint32_t* const* d_pages, int32_t n_ranks, int32_t me, uint32_t epoch, uint64_t max_polls,
+int bddl_flag_barrier(uint32_t* const* d_pages, int32_t n_ranks, int32_t me, uint32_t epoch, uint64_t timeout_ns,
                       const uint32_t* d_stop, uint32_t* d_status, void* stream) {
     if (!d_pages || n_ranks < 1 || n_ranks > 1024 || me < 0 || me >= n_ranks)
         return bddl_fail(BDDL_ERR_INVALID, "flag_barrier: bad arguments");
     int threads = ((n_ranks + 31) / 32) * 32;
-    flag_barrier_kernel<<<1, threads, 0, (cudaStream_t)stream>>>(d_pages, n_ranks, me, epoch,
-                                                                 max_polls ? max_polls : ~0ULL, d_stop, d_status);
+    flag_barrier_kernel<<<1, threads, 0, (cudaStream_t)stream>>>(d_pages, n_ranks, me, epoch, timeout_ns,
+                                                                 d_stop, d_status);
     bddl_count_launch(1);
     BDDL_CUDA(cudaGetLastError());
     return 0;

@@ -347,19 +347,27 @@ __device__ __forceinline__ uint4 convert_group_uniform(const uint8_t* src, float
 
 // Groups [g0, g1) of a chunk, one channel: the hot loop (per 8 pixels of the uint8 -> bf16 form:
 // one LDS.64, 8 PRMT, 8 FFMA, 8 FADD, 4 packs, one STG.128; 32-bit index arithmetic).
-template <int MODE, bool G, int UNROLL>
+template <bool MC>
+__device__ __forceinline__ void store16(uint8_t* dst, uint4 v) {
+    if constexpr (MC)
+        st_multimem_v4(dst, v);  // dst is a multicast mapping: one store, every GPU's copy
+    else
+        *reinterpret_cast<uint4*>(dst) = v;
+}
+
+template <int MODE, bool G, int UNROLL, bool MC>
 __device__ __forceinline__ void convert_span(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, uint32_t g0,
                                              uint32_t g1, int lane, float sc, float no, float bi) {
     using C = Cvt<MODE>;
 #pragma unroll UNROLL
     for (uint32_t g = g0 + lane; g < g1; g += 32) {
         const uint4 v = convert_group_uniform<MODE, G>(src + g * (uint32_t)(C::PER * C::IN_ES), sc, no, bi);
-        *reinterpret_cast<uint4*>(dst + g * 16u) = v;
+        store16<MC>(dst + g * 16u, v);
     }
 }
 
 // Convert the payload of one chunk (src: shared or global) and pad the rest of its region.
-template <int MODE, bool CHAN, bool G, int UNROLL, uint32_t CHUNK_ELEMS>
+template <int MODE, bool CHAN, bool G, int UNROLL, uint32_t CHUNK_ELEMS, bool MC = false>
 __device__ __forceinline__ void convert_chunk(const KParams& p, const uint8_t* __restrict__ src,
                                               const Item& it, int lane) {
     using C = Cvt<MODE>;
@@ -371,27 +379,28 @@ __device__ __forceinline__ void convert_chunk(const KParams& p, const uint8_t* _
         // a chunk touches at most two channels: [0, gb) is the first, the group that straddles the
         // boundary (if any) goes through the per-element selects, the rest is the second channel
         const uint32_t gb = CHAN ? min(n_groups, cx.boundary / (uint32_t)C::PER) : n_groups;
-        convert_span<MODE, G, UNROLL>(src, dst, 0, gb, lane, cx.sc0, cx.no0, cx.bi0);
+        convert_span<MODE, G, UNROLL, MC>(src, dst, 0, gb, lane, cx.sc0, cx.no0, cx.bi0);
         if (CHAN && gb < n_groups) {
             uint32_t g2 = gb;
             if (cx.boundary % (uint32_t)C::PER) {
                 if (lane == 0) {
                     const uint4 v = convert_group<MODE, CHAN, G>(p, cx, src + gb * (uint32_t)(C::PER * C::IN_ES),
                                                                  gb * C::PER, it.elem0 + gb * C::PER);
-                    *reinterpret_cast<uint4*>(dst + gb * 16u) = v;
+                    store16<MC>(dst + gb * 16u, v);
                 }
                 g2 = gb + 1;
             }
-            convert_span<MODE, G, UNROLL>(src, dst, g2, n_groups, lane, cx.sc1, cx.no1, cx.bi1);
+            convert_span<MODE, G, UNROLL, MC>(src, dst, g2, n_groups, lane, cx.sc1, cx.no1, cx.bi1);
         }
     } else {
 #pragma unroll UNROLL
         for (uint32_t g = lane; g < n_groups; g += 32) {
             const uint4 v = convert_group<MODE, CHAN, G>(p, cx, src + (size_t)g * (C::PER * C::IN_ES), g * C::PER,
                                                          it.elem0 + g * C::PER);
-            *reinterpret_cast<uint4*>(dst + (size_t)g * 16) = v;
+            store16<MC>(dst + (size_t)g * 16, v);
         }
     }
+    if constexpr (MC) return;  // multicast rows are whole 16-byte groups (checked by the launcher)
     const uint32_t done = n_groups * C::PER;
     for (uint32_t e = done + lane; e < n_elems; e += 32)
         convert_one<MODE, CHAN, G>(p, src + (size_t)e * C::IN_ES, dst + (size_t)e * C::OUT_ES, it.elem0 + e);
@@ -426,7 +435,7 @@ __global__ void __launch_bounds__(kWarps * 32) gather_ldg_kernel(const __grid_co
 // One warp's pipeline over its private ring of STAGES chunks: lane 0 keeps STAGES bulk loads in
 // flight, the warp converts a landed stage straight into the batch tensor and re-arms the stage.
 // item_at(k) names the warp's k-th work item.
-template <int MODE, bool CHAN, int CHUNK, int STAGES, typename ItemAt>
+template <int MODE, bool CHAN, int CHUNK, int STAGES, bool MC = false, typename ItemAt>
 __device__ __forceinline__ void warp_pipeline(const KParams& p, uint8_t* ring, uint64_t* full, uint32_t n_my,
                                               int lane, ItemAt item_at) {
     auto issue = [&](uint32_t k) {
@@ -449,7 +458,7 @@ __device__ __forceinline__ void warp_pipeline(const KParams& p, uint8_t* ring, u
             mbar_wait(full + s, (phase >> s) & 1u);
             phase ^= 1u << s;
         }
-        convert_chunk<MODE, CHAN, false, 4, CHUNK / Cvt<MODE>::IN_ES>(p, ring + (size_t)s * CHUNK, it, lane);
+        convert_chunk<MODE, CHAN, false, 4, CHUNK / Cvt<MODE>::IN_ES, MC>(p, ring + (size_t)s * CHUNK, it, lane);
         __syncwarp();
         if (lane == 0 && k + STAGES < n_my) {
             fence_proxy_async_smem();  // the warp's reads of this stage precede the next bulk write
@@ -500,28 +509,23 @@ struct PushParams {
     const uint64_t* const* tables;  // [n_ranks] every consumer's slot-table buffer (peer mappings)
     uint8_t* const* rings;          // [n_ranks] every consumer's batch ring (peer mappings)
     uint32_t* const* flags;         // [n_ranks] every rank's flag page (peer mappings)
+    uint8_t* mc_ring;               // multicast mapping of the rings (replicated windows), or null
     int64_t table_off;              // byte offset of the window slice inside a table buffer
     int64_t ring_off;               // byte offset of the ring slot inside a ring
-    unsigned long long max_polls;
-    uint32_t* status;               // 0 ok, 1 timed out, 2 stopped
+    unsigned long long timeout_ns;
+    uint32_t* status;               // outcome | which wait << 4 | peer << 8
     int32_t n_ranks, me, ctas_per_consumer;
+    int32_t table_rank;             // replicated window: every consumer gets this rank's window; -1 = its own
     uint32_t owner_lo, owner_hi;    // source ids this GPU owns
     uint32_t ready_word, free_word0, table_word0, done_word0, stop_word;
     uint32_t free_need, table_need, ready_need, done_target;
 };
 
-__device__ __forceinline__ uint32_t poll_geq(const uint32_t* flag, uint32_t need, const uint32_t* stop,
-                                             unsigned long long max_polls) {
-    unsigned long long polls = 0;
-    while ((int32_t)(ld_acquire_sys_u32(flag) - need) < 0) {
-        if (ld_acquire_sys_u32(stop) != 0) return 2;
-        if (++polls >= max_polls) return 1;
-        __nanosleep(200);
-    }
-    return 0;
-}
-
-template <int MODE, bool CHAN, int CHUNK, int STAGES, int NW>
+// MC = true: a replicated window delivered through the NVLS multicast mapping of the rings -- the
+// whole grid is one group, every sample this GPU owns is converted once and stored once
+// (multimem.st), NVSwitch writes it into every consumer's ring slot, and the last CTA bumps every
+// consumer's `ready` word.
+template <int MODE, bool CHAN, int CHUNK, int STAGES, int NW, bool MC>
 __global__ void __launch_bounds__(NW * 32) push_tma_cvt_kernel(const __grid_constant__ KParams p,
                                                                const __grid_constant__ PushParams q) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -533,10 +537,11 @@ __global__ void __launch_bounds__(NW * 32) push_tma_cvt_kernel(const __grid_cons
     uint64_t* slot_of = reinterpret_cast<uint64_t*>(ctrl + 4);         // [n_samples] the consumer's slice
     uint16_t* mine = reinterpret_cast<uint16_t*>(slot_of + p.n_samples);  // batch rows this GPU owns
 
-    const int G = q.ctas_per_consumer;
-    const int group = blockIdx.x / G;
+    const int G = MC ? (int)gridDim.x : q.ctas_per_consumer;
+    const int group = MC ? 0 : blockIdx.x / G;
     const int lc = blockIdx.x - group * G;
     const int c = (q.me + group) % q.n_ranks;  // staggered: owners do not all start on one consumer
+    const int tr = q.table_rank >= 0 ? q.table_rank : c;  // whose window this consumer receives
     uint32_t* my_page = q.flags[q.me];
     const uint32_t* stop = my_page + q.stop_word;
 
@@ -545,21 +550,24 @@ __global__ void __launch_bounds__(NW * 32) push_tma_cvt_kernel(const __grid_cons
         for (int s = 0; s < STAGES; ++s) mbar_init(full + s, 1);
         fence_mbar_init();
     }
-    if (threadIdx.x == 0) {
+    if (threadIdx.x == 0) ctrl[0] = 0;
+    __syncthreads();
+    // status = outcome (1 timed out, 2 stopped) | which wait (1 free, 2 table, 3 ready) << 4 | peer << 8
+    if (threadIdx.x < (MC ? q.n_ranks : 1)) {
+        const int peer = MC ? (int)threadIdx.x : c;  // multicast stores land in every consumer's slot
         uint32_t st = 0;
-        // status = outcome (1 timed out, 2 stopped) | which wait (1 free, 2 table, 3 ready) << 4 | peer << 8
-        if (q.free_need) st = poll_geq(my_page + q.free_word0 + c, q.free_need, stop, q.max_polls);
-        if (st) st |= (1u << 4) | ((uint32_t)c << 8);
-        if (!st) {
-            st = poll_geq(my_page + q.table_word0 + c, q.table_need, stop, q.max_polls);
-            if (st) st |= (2u << 4) | ((uint32_t)c << 8);
+        if (q.free_need) st = poll_geq(my_page + q.free_word0 + peer, q.free_need, stop, q.timeout_ns);
+        if (st) st |= (1u << 4) | ((uint32_t)peer << 8);
+        if (!st && threadIdx.x == 0) {
+            st = poll_geq(my_page + q.table_word0 + tr, q.table_need, stop, q.timeout_ns);
+            if (st) st |= (2u << 4) | ((uint32_t)tr << 8);
         }
-        ctrl[0] = st;
+        if (st) atomicMax(ctrl, st);
     }
     __syncthreads();
     uint32_t st = ctrl[0];
     if (st == 0) {
-        const uint64_t* theirs = reinterpret_cast<const uint64_t*>(reinterpret_cast<const uint8_t*>(q.tables[c]) +
+        const uint64_t* theirs = reinterpret_cast<const uint64_t*>(reinterpret_cast<const uint8_t*>(q.tables[tr]) +
                                                                    q.table_off);
         for (uint32_t i = threadIdx.x; i < p.n_samples; i += NW * 32) slot_of[i] = __ldcg(theirs + i);
         __syncthreads();
@@ -584,8 +592,8 @@ __global__ void __launch_bounds__(NW * 32) push_tma_cvt_kernel(const __grid_cons
         const uint32_t gw = lc * NW + warp;
         const uint32_t nw = G * NW;
         const uint32_t n_my = gw < n_items ? (n_items - gw + nw - 1) / nw : 0;
-        uint8_t* dst = q.rings[c] + q.ring_off;
-        warp_pipeline<MODE, CHAN, CHUNK, STAGES>(p, ring, full, n_my, lane, [&](uint32_t k) {
+        uint8_t* dst = (MC ? q.mc_ring : q.rings[c]) + q.ring_off;
+        warp_pipeline<MODE, CHAN, CHUNK, STAGES, MC>(p, ring, full, n_my, lane, [&](uint32_t k) {
             const uint32_t item = gw + k * nw;
             const uint32_t ch = item / n_mine;
             const uint32_t s = mine[item - ch * n_mine];
@@ -593,21 +601,30 @@ __global__ void __launch_bounds__(NW * 32) push_tma_cvt_kernel(const __grid_cons
         });
         __syncthreads();
         if (threadIdx.x == 0) {
-            __threadfence_system();  // this CTA's stores into the consumer's ring are visible system-wide
-            const uint32_t t = atomicAdd(my_page + q.done_word0 + c, 1u) + 1u;
+            __threadfence_system();  // this CTA's stores into the consumers' rings are visible system-wide
+            const uint32_t t = atomicAdd(my_page + q.done_word0 + (MC ? 0 : c), 1u) + 1u;
             if (t == q.done_target) {  // last CTA of the group: every CTA's stores precede the token
                 __threadfence_system();
-                red_release_sys_add_u32(q.flags[c] + q.ready_word, 1u);
+                if (MC) {
+                    for (int r = 0; r < q.n_ranks; ++r) red_release_sys_add_u32(q.flags[r] + q.ready_word, 1u);
+                } else {
+                    red_release_sys_add_u32(q.flags[c] + q.ready_word, 1u);
+                }
             }
         }
     }
     // status may live in mapped host memory (the loader reads it without synchronising): a plain
     // release store; any non-zero value says that a bounded wait gave up
     if (blockIdx.x == 0 && threadIdx.x == 0 && st == 0) {
-        st = poll_geq(my_page + q.ready_word, q.ready_need, stop, q.max_polls);
+        st = poll_geq(my_page + q.ready_word, q.ready_need, stop, q.timeout_ns);
         if (st) st |= (3u << 4) | ((uint32_t)q.me << 8);
     }
-    if (st && threadIdx.x == 0) st_release_sys_u32(q.status, st);
+    if (st && threadIdx.x == 0) {
+        st_release_sys_u32(q.status, st);
+        // a wait gave up: set this rank's stop word so that the launches already queued behind this
+        // one return at once instead of timing out one after the other
+        st_release_sys_u32(my_page + q.stop_word, 1u);
+    }
 }
 
 // ---- TMA / copy form ---------------------------------------------------------------------------
@@ -768,8 +785,8 @@ int launch_mode(const bddl_gather_desc* d, KParams& p, bool tma, cudaStream_t st
     }
 }
 
-template <int MODE, bool CHAN>
-int launch_push(const bddl_gather_desc* d, KParams& p, PushParams& q, cudaStream_t st) {
+template <int MODE, bool CHAN, bool MC>
+int launch_push_as(const bddl_gather_desc* d, KParams& p, PushParams& q, cudaStream_t st) {
     constexpr int CHUNK = 4096, STAGES = 3, NW = 16;
     const size_t smem = (size_t)NW * STAGES * CHUNK + (size_t)NW * STAGES * sizeof(uint64_t) + 16 +
                         (size_t)d->n_samples * (sizeof(uint64_t) + sizeof(uint16_t));
@@ -779,7 +796,7 @@ int launch_push(const bddl_gather_desc* d, KParams& p, PushParams& q, cudaStream
     static bool configured[64];
     int dev = 0;
     BDDL_CUDA(cudaGetDevice(&dev));
-    auto kernel = push_tma_cvt_kernel<MODE, CHAN, CHUNK, STAGES, NW>;
+    auto kernel = push_tma_cvt_kernel<MODE, CHAN, CHUNK, STAGES, NW, MC>;
     if (!configured[dev & 63]) {
         int rc = set_smem(kernel, 227 * 1024);
         if (rc) return rc;
@@ -791,6 +808,11 @@ int launch_push(const bddl_gather_desc* d, KParams& p, PushParams& q, cudaStream
     bddl_count_launch(1);
     BDDL_CUDA(cudaGetLastError());
     return 0;
+}
+
+template <int MODE, bool CHAN>
+int launch_push(const bddl_gather_desc* d, KParams& p, PushParams& q, cudaStream_t st) {
+    return q.mc_ring ? launch_push_as<MODE, CHAN, true>(d, p, q, st) : launch_push_as<MODE, CHAN, false>(d, p, q, st);
 }
 
 }  // namespace
@@ -933,9 +955,19 @@ extern "C" int bddl_exchange_push_collate(const bddl_gather_desc* d, const bddl_
     q.tables = (const uint64_t* const*)u->d_tables;
     q.rings = (uint8_t* const*)u->d_rings;
     q.flags = (uint32_t* const*)u->d_flags;
+    q.mc_ring = (uint8_t*)u->d_mc_ring;
+    q.table_rank = u->table_rank;
+    if (u->table_rank >= u->n_ranks) return bddl_fail(BDDL_ERR_INVALID, "push: table_rank out of range");
+    if (u->d_mc_ring) {
+        static const int group_in[] = {16, 8, 32, 4, 8};  // input bytes of one 16-byte output group
+        if (var || d->sample_bytes % group_in[d->mode] || ((uintptr_t)u->d_mc_ring & 15))
+            return bddl_fail(BDDL_ERR_UNSUPPORTED, "push: multicast delivery needs fixed-size rows of whole 16-byte "
+                                                   "output groups");
+        if (u->table_rank < 0) return bddl_fail(BDDL_ERR_INVALID, "push: multicast delivery is for replicated windows");
+    }
     q.table_off = u->table_offset_bytes;
     q.ring_off = u->ring_offset_bytes;
-    q.max_polls = u->max_polls ? u->max_polls : ~0ULL;
+    q.timeout_ns = u->timeout_ns;
     q.status = u->d_status;
     q.n_ranks = u->n_ranks;
     q.me = u->me;
@@ -944,13 +976,14 @@ extern "C" int bddl_exchange_push_collate(const bddl_gather_desc* d, const bddl_
     q.owner_hi = (uint32_t)u->owner_hi;
     q.ready_word = BDDL_FLAG_READY0 + u->ring_slot;
     q.free_word0 = BDDL_FLAG_FREE0 + u->ring_slot * BDDL_FLAG_MAX_RANKS;
-    q.done_word0 = BDDL_FLAG_DONE0 + u->ring_slot * BDDL_FLAG_MAX_RANKS;
+    q.done_word0 = u->d_mc_ring ? BDDL_FLAG_DONE_MC0 + u->ring_slot : BDDL_FLAG_DONE0 + u->ring_slot * BDDL_FLAG_MAX_RANKS;
     q.table_word0 = BDDL_FLAG_TABLE0 + u->window * BDDL_FLAG_MAX_RANKS;
     q.stop_word = BDDL_FLAG_STOP;
     q.free_need = u->use;  // the slot's previous contents (its use-th fill) have been consumed
     q.table_need = u->table_seq;
     q.ready_need = (u->use + 1) * (uint32_t)u->n_ranks;  // every owner bumps `ready` once per fill
-    q.done_target = (u->use + 1) * (uint32_t)u->ctas_per_consumer;
+    // tickets are monotonic per (slot, group kind): `fills` earlier launches of this kind used the slot
+    q.done_target = (u->fills + 1) * (uint32_t)(u->d_mc_ring ? u->n_ranks * u->ctas_per_consumer : u->ctas_per_consumer);
     cudaStream_t st = (cudaStream_t)stream;
     switch (d->mode) {
         case BDDL_CVT_COPY:

@@ -69,6 +69,18 @@ int bddl_memcpy_async(void* dst, const void* src, size_t bytes, int32_t kind, vo
     return 0;
 }
 
+// Strided rows in one call (K1 shard_load: a pinned window whose rows are padded to the shard's
+// 16-byte row stride on the way into HBM).
+int bddl_memcpy2d_async(void* dst, size_t dst_pitch, const void* src, size_t src_pitch, size_t width_bytes,
+                        size_t rows, int32_t kind, void* stream) {
+    cudaMemcpyKind k = kind == 1   ? cudaMemcpyHostToDevice
+                       : kind == 2 ? cudaMemcpyDeviceToHost
+                       : kind == 3 ? cudaMemcpyDeviceToDevice
+                                   : cudaMemcpyDefault;
+    BDDL_CUDA(cudaMemcpy2DAsync(dst, dst_pitch, src, src_pitch, width_bytes, rows, k, (cudaStream_t)stream));
+    return 0;
+}
+
 int bddl_stream_synchronize(void* stream) {
     BDDL_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     return 0;

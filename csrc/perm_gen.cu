@@ -6,10 +6,10 @@
 //
 // numpy's shuffle is "for i = n-1 .. 1: j = bounded_draw(i); swap(t[i], t[j])" with masked
 // rejection on a stream of 32-bit draws -- sequential as written.  One CTA of
-// 1024 threads per table runs it in two parallel phases that give the same result bit for bit:
+// 512 threads per table runs it in two parallel phases that give the same result bit for bit:
 //
 //   A. targets.  PCG64 is an LCG, so thread t jumps straight to output t of the current batch
-//      (2048 draws per batch).  Whether draw k is accepted depends only on how many earlier draws
+//      (1024 draws per batch).  Whether draw k is accepted depends only on how many earlier draws
 //      of the batch were (that fixes the index it is drawn for, hence the mask and the bound), so
 //      accept/reject of the whole batch is the unique fixed point of "scan the accept bits,
 //      re-evaluate" -- a few block-wide scans (2-6 rounds; more only in the last few thousand
@@ -36,7 +36,7 @@
 
 namespace {
 
-constexpr int kThreads = 1024;
+constexpr int kThreads = 512;  // + <= 64 registers: co-resides with a 512-thread batch-assembly CTA on one SM
 constexpr int kWarps = kThreads / 32;
 
 struct Ctl {
@@ -58,7 +58,7 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t x, Ctl& c, uint32_t
     __syncthreads();  // the previous scan's warp_sum has been read by everyone
     if (lane == 31) c.warp_sum[warp] = incl;
     __syncthreads();
-    uint32_t w = c.warp_sum[lane];
+    uint32_t w = lane < kWarps ? c.warp_sum[lane] : 0u;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const uint32_t y = __shfl_up_sync(0xffffffffu, w, o);

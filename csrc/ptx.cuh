@@ -93,6 +93,37 @@ __device__ __forceinline__ void red_release_sys_add_u32(uint32_t* p, uint32_t v)
     asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(__cvta_generic_to_global(p)), "r"(v) : "memory");
 }
 
+// 16-byte store through an NVLS multicast mapping: NVSwitch replicates it into every bound GPU's memory.
+__device__ __forceinline__ void st_multimem_v4(void* mc_ptr, uint4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(__cvta_generic_to_global(mc_ptr)),
+                 "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)),
+                 "f"(__uint_as_float(v.w))
+                 : "memory");
+}
+
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// Bounded acquire-poll of a counter that a peer (or the host) advances: 0 = reached `need`,
+// 1 = `timeout_ns` passed (0 = no limit), 2 = the stop word was set.
+__device__ __forceinline__ uint32_t poll_geq(const uint32_t* flag, uint32_t need, const uint32_t* stop,
+                                             unsigned long long timeout_ns) {
+    if ((int32_t)(ld_acquire_sys_u32(flag) - need) >= 0) return 0;
+    const unsigned long long t0 = global_timer_ns();
+    uint32_t spins = 0;
+    while ((int32_t)(ld_acquire_sys_u32(flag) - need) < 0) {
+        if ((++spins & 63u) == 0) {
+            if (stop && ld_acquire_sys_u32(stop) != 0) return 2;
+            if (timeout_ns && global_timer_ns() - t0 > timeout_ns) return 1;
+        }
+        __nanosleep(100);
+    }
+    return 0;
+}
+
 __device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
     uint4 v;
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"

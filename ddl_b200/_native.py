@@ -90,7 +90,7 @@ class PushDesc(C.Structure):
         ("d_flags", C.c_void_p),
         ("table_offset_bytes", C.c_int64),
         ("ring_offset_bytes", C.c_int64),
-        ("max_polls", C.c_uint64),
+        ("timeout_ns", C.c_uint64),
         ("d_status", C.c_void_p),
         ("n_ranks", C.c_int32),
         ("me", C.c_int32),
@@ -101,6 +101,9 @@ class PushDesc(C.Structure):
         ("ctas_per_consumer", C.c_int32),
         ("use", C.c_uint32),
         ("table_seq", C.c_uint32),
+        ("d_mc_ring", C.c_void_p),
+        ("table_rank", C.c_int32),
+        ("fills", C.c_uint32),
     ]
 
 
@@ -145,6 +148,7 @@ def _declare(lib: C.CDLL) -> None:
         "bddl_free": (C.c_int, [vp]),
         "bddl_memset_async": (C.c_int, [vp, C.c_int, sz, vp]),
         "bddl_memcpy_async": (C.c_int, [vp, vp, sz, i32, vp]),
+        "bddl_memcpy2d_async": (C.c_int, [vp, sz, vp, sz, sz, sz, i32, vp]),
         "bddl_stream_synchronize": (C.c_int, [vp]),
         "bddl_event_create": (C.c_int, [P(vp)]),
         "bddl_event_destroy": (C.c_int, [vp]),

@@ -37,6 +37,10 @@ class LoaderConfig:
     # step).  push: each owner's kernel stores the samples it owns into every consumer's ring slot
     # and signals `ready` from inside the kernel; all consumers must step in lock-step.
     exchange: str = "pull"
+    # push form: allocate the batch rings with the VMM API and bind them to an NVLS multicast object
+    # so that replicated windows are delivered with one multimem.st per 16 bytes.  "auto" = where the
+    # platform supports it, "on" = required, "off" = cudaMalloc rings, replicated windows unicast.
+    multicast: str = "auto"
     host_pull: bool = False        # process transport: kernel reads the pinned window directly
     residency: str = "hbm"         # device transport: shards in "hbm" or in pinned "host" memory
     # host residency: "gather" (threaded CPU gather into a pinned buffer + one cudaMemcpyAsync),
@@ -53,6 +57,12 @@ class LoaderConfig:
     # second time by the independent LDG form of the kernel and the two fingerprints are compared
     verify: bool = False
     trace: bool = False            # CUDA-event timing of every loader stage
+    # debug canaries: every ring slot is stamped (lend number, batch index) on the
+    # fetch stream right behind its assembly; the stamp is checked when the batch is handed out and
+    # again when it is marked, so a slot that is refilled while the training loop still holds it, or
+    # handed out before its assembly finished, raises instead of corrupting a step silently.
+    # Synchronises per batch: a debugging aid, like compute-sanitizer's racecheck would be.
+    canary: bool = False
 
     def __post_init__(self) -> None:
         self.validate()  # also configs built directly (not through from_env) are checked
@@ -82,6 +92,8 @@ class LoaderConfig:
             raise ValueError(f"unknown shuffle_mode {self.shuffle_mode!r}")
         if self.barrier not in ("auto", "nccl", "flags", "host"):
             raise ValueError(f"unknown barrier {self.barrier!r}")
+        if self.multicast not in ("auto", "on", "off"):
+            raise ValueError(f"multicast must be 'auto', 'on' or 'off', not {self.multicast!r}")
         if self.exchange not in ("pull", "push"):
             raise ValueError(f"unknown exchange {self.exchange!r}")
         if self.residency not in ("hbm", "host") or self.host_stage not in ("gather", "memcpy", "pull"):

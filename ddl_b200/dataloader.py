@@ -87,6 +87,7 @@ class DistributedDataLoader(DistributedDataloaderABC):
         self._verify_pending: list = []
         self._cur_slot = -1
         self._next_slot = 0
+        self._canary = None
 
         if connection is None:  # single process, no decorator: build the one-rank world here
             from .parallel.topology import init_env
@@ -136,6 +137,9 @@ class DistributedDataLoader(DistributedDataloaderABC):
         self.batches_per_window = [m.batches_per_window for m in self.metadata_from_producer]
         specs = [WindowSpec(m, self.cfg.seq_rank, self.cfg.seq_size) for m in self.metadata_from_producer]
         self.splits = [s.splits for s in specs]
+        if any(s.replicate for s in specs) and self.cfg.exchange != "push" and env.n_instances > 1:
+            raise ValueError("replicated windows (replicate=True) are delivered by the push form: "
+                             "use LoaderConfig(exchange='push')")
         self.engine = DeviceEngine(env, self.cfg, specs, self.batch_size)
         conn.attach(self.engine, pushers)
         for p in pushers:
@@ -151,7 +155,9 @@ class DistributedDataLoader(DistributedDataloaderABC):
         # the one-call hot path covers the product's main configuration; everything else
         # (push form, host staging, tracing, integrity mode, metrics) takes the general path
         self._fast = (eng.cuda and not eng.push and eng.stage is None and not self.cfg.trace
-                      and not self.cfg.verify)
+                      and not self.cfg.verify and not self.cfg.canary)
+        self._canary = (torch.zeros((eng.ring_depth, 2), dtype=torch.int32, device=self.device)
+                        if self.cfg.canary else None)
         self._views = {}
         self.main = eng.main
         self.fetch = eng.fetch
@@ -250,6 +256,9 @@ class DistributedDataLoader(DistributedDataloaderABC):
             self.metrics.stall(time.perf_counter() - t0)
         stream_wait(self._train_stream(), ev)  # whichever stream the training step runs on
         self._cur_slot, self._cur_batch = slot, b
+        if self._canary is not None:
+            ev.synchronize()
+            self._check_canary("handed out")
         if self.cfg.prefetch:
             for d in range(1, self.cfg.prefetch_depth + 1):
                 if b + d < self.batches_per_window[k]:
@@ -304,6 +313,8 @@ class DistributedDataLoader(DistributedDataloaderABC):
             if self.cfg.verify and eng.cuda and not eng.push and eng.stage is None:
                 self._verify_pending.append((b, eng.verify_batch(k, self.connection.pushers[k].lent_buf, b * B,
                                                                  slot, stream)))
+            if self._canary is not None:
+                self._stamp(slot, b, stream)
             ev = self._done[slot]
             if eng.cuda:
                 ev.record(stream)
@@ -368,9 +379,31 @@ class DistributedDataLoader(DistributedDataloaderABC):
                 raise RuntimeError(f"integrity check failed for batch {b}: TMA and LDG forms of "
                                    f"exchange_gather_collate disagree ({x:#x} != {y:#x})")
 
+    # -- debug canaries -------------------------------------------------------------------------------------
+    def _stamp(self, slot: int, b: int, stream) -> None:
+        """(lend number, batch index) into the slot's canary words, ordered behind its assembly."""
+        want = (self._lend_seq & 0x7FFFFFFF, b)
+        if self.cuda:
+            base = self._canary[slot].data_ptr()
+            for i, v in enumerate(want):
+                N.check(N.lib().bddl_stream_write_value32(C.c_void_p(stream.cuda_stream), C.c_void_p(base + 4 * i), v))
+        else:
+            self._canary[slot, 0], self._canary[slot, 1] = want
+
+    def _check_canary(self, when: str) -> None:
+        if self.cuda:
+            self._train_stream().synchronize()
+        got = tuple(int(v) for v in self._canary[self._cur_slot].tolist())
+        want = (self._lend_seq & 0x7FFFFFFF, self._cur_batch)
+        if got != want:
+            raise RuntimeError(f"canary: ring slot {self._cur_slot} holds (lend, batch) = {got} but {want} was "
+                               f"{when}: the slot was refilled while in use, or handed out before it was assembled")
+
     def _on_batch_end(self) -> None:
         if self._verify_pending:
             self._check_verified()
+        if self._canary is not None and self._cur_slot >= 0:
+            self._check_canary("being marked")
         if self._cur_slot >= 0 and not isinstance(self.main, NullStream):
             ev = self._consumed[self._cur_slot]
             if ev is None:
@@ -482,8 +515,16 @@ class DistributedDataLoader(DistributedDataloaderABC):
         first = self._cur_batch * B
         if eng.cuda:
             eng.side.synchronize()
-        slots = eng.tables[k, buf, first:first + B].cpu().numpy()
         s = eng.specs[k]
+        if s.replicate and eng.n_instances > 1 and eng.cuda:
+            # a replicated window delivers instance 0's table: read that slice through its peer mapping
+            mine = torch.empty(B, dtype=torch.int64, device=self.device)
+            N.check(N.lib().bddl_memcpy_async(C.c_void_p(mine.data_ptr()),
+                                              C.c_void_p(eng.heap.peer_ptr(0, "tables") + ((k * 2 + buf) * eng.n_max + first) * 8),
+                                              B * 8, 4, C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+            slots = mine.cpu().numpy()
+        else:
+            slots = eng.tables[k, buf, first:first + B].cpu().numpy()
         raw = eng.reference_rows(k, slots)
         lens = eng.batch_lengths(k, buf, first, B) if s.var else None
         y = convert_reference(raw, s.convert, lens, copy_elem_size=s.np_dtype.itemsize)

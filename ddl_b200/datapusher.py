@@ -36,7 +36,8 @@ def _meta_from_init(ret: DataProducerOnInitReturn, batch_size: int) -> MetaData_
     return MetaData_Producer_To_Consumer(
         nData=ret.nData, nValues=ret.nValues, shape=tuple(ret.shape), splits=tuple(ret.splits),
         batches_per_window=bpw, dtype=getattr(ret, "dtype", np.float32), convert=getattr(ret, "convert", None),
-        shuffle_seed=getattr(ret, "shuffle_seed", None), variable_length=getattr(ret, "variable_length", False))
+        shuffle_seed=getattr(ret, "shuffle_seed", None), variable_length=getattr(ret, "variable_length", False),
+        replicate=getattr(ret, "replicate", False))
 
 
 def _private_copy(obj):

@@ -133,6 +133,7 @@ class WindowSpec:
         self.convert: Convert = meta.convert if meta.convert is not None else Convert.copy()
         self.splits = tuple(int(s) for s in meta.splits) if seq_size == 1 else (self.nValues,)
         self.var = bool(getattr(meta, "variable_length", False))
+        self.replicate = bool(getattr(meta, "replicate", False))
         if self.convert.mode == N.CVT_COPY:
             self.out_dtype = _TORCH_OF_NP[self.np_dtype]
             self.out_elem = self.np_dtype.itemsize
@@ -260,7 +261,7 @@ class DeviceEngine:
         self.flags_buf = self.heap.alloc("flags", N.FLAG_PAGE_BYTES)
         ring_row = max(s.dst_row_bytes for s in specs)
         self.ring_depth = config.ring_depth
-        self.ring_buf = self.heap.alloc("ring", self.ring_depth * self.B * ring_row, zero=False)
+        self.ring_buf = self._alloc_ring(self.ring_depth * self.B * ring_row)
         self.heap.publish()
 
         self.tables = self.tables_buf.tensor(torch.int64, (self.P, 2, self.n_max))
@@ -272,7 +273,9 @@ class DeviceEngine:
 
         if self.cuda:
             self.main = torch.cuda.current_stream(self.device)
-            self.side = torch.cuda.Stream(self.device, priority=0)      # table production
+            # table production: few, small kernels that everything else eventually waits for -> high
+            # priority, so that they get the next free SM even while batch assembly fills the GPU
+            self.side = torch.cuda.Stream(self.device, priority=-1)
             self.fetch_streams = [torch.cuda.Stream(self.device, priority=config.fetch_priority)
                                   for _ in range(config.fetch_streams)]  # batch assembly
             self.fetch = self.fetch_streams[0]
@@ -332,6 +335,27 @@ class DeviceEngine:
         self._flag_pages = None
         self._closed = False
 
+    def _alloc_ring(self, nbytes: int):
+        """The batch ring.  For the push form it is made with the VMM API where possible, mapped by
+        every peer and bound to an NVLS multicast object (replicated windows); otherwise cudaMalloc +
+        CUDA IPC like every other heap buffer."""
+        want = (self.cfg.exchange == "push" and self.cuda and self.cfg.residency != "host"
+                and self.cfg.multicast != "off" and self.n_instances > 1)
+        if want:
+            try:
+                return self.heap.alloc_vmm("ring", nbytes, multicast=True)
+            except N.NativeError as e:
+                ok = False
+                if self.cfg.multicast == "on":
+                    raise
+                log.info("VMM ring unavailable (%s); using a cudaMalloc ring", e)
+            # a rank without VMM support raises before any collective step of alloc_vmm: all ranks
+            # take the same branch because the capability query is the same on one box
+            del ok
+        if self.cfg.multicast == "on" and self.cfg.exchange == "push" and self.n_instances > 1:
+            raise RuntimeError("multicast='on' needs CUDA devices with VMM and NVLS multicast support")
+        return self.heap.alloc("ring", nbytes, zero=False)
+
     # -- helpers --------------------------------------------------------------------------------
     def event(self):
         return NativeEvent() if self.cuda else NullEvent()
@@ -371,11 +395,17 @@ class DeviceEngine:
         if self.host_resident:
             dst[:, :s.window_bytes] = src
         elif self.cuda:
-            with torch.cuda.stream(st):
-                if s.row_bytes == s.window_bytes:
-                    dst.copy_(src, non_blocking=True)
-                else:
-                    dst[:, :s.window_bytes].copy_(src, non_blocking=True)
+            # K1 shard_load: the window is pinned (cudaHostAlloc), so this is a true asynchronous
+            # DMA on the side stream -- one cudaMemcpyAsync, or one strided copy when the shard's
+            # rows are padded to 16 bytes
+            lib, sp = N.lib(), C.c_void_p(st.cuda_stream)
+            if s.row_bytes == s.window_bytes:
+                N.check(lib.bddl_memcpy_async(C.c_void_p(self.shards[k].ptr), C.c_void_p(window.ctypes.data),
+                                              s.nData * s.window_bytes, 1, sp))
+            else:
+                N.check(lib.bddl_memcpy2d_async(C.c_void_p(self.shards[k].ptr), s.row_bytes,
+                                                C.c_void_p(window.ctypes.data), s.window_bytes, s.window_bytes,
+                                                s.nData, 1, sp))
         else:
             dst[:, :s.window_bytes] = src
 
@@ -510,9 +540,8 @@ class DeviceEngine:
             self._status_word()
         self.check_waits()
         self._barrier_epoch += 1
-        polls = int(self.cfg.timeout_s * 2e6)
         N.check(N.lib().bddl_flag_barrier(self._flag_pages.data_ptr(), self.n_instances, self.me,
-                                          self._barrier_epoch, polls, None, C.c_void_p(self._status_dev),
+                                          self._barrier_epoch, int(self.cfg.timeout_s * 1e9), None, C.c_void_p(self._status_dev),
                                           C.c_void_p(self.side.cuda_stream)))
         self.launches += 1
 
@@ -629,6 +658,11 @@ class DeviceEngine:
         if self.remote_storage:
             raise NotImplementedError("the push form needs the shards on the consumer GPUs (no storage ranks)")
         self._use = [0] * D
+        self._fills = {False: [0] * D, True: [0] * D}  # per slot: launches so far, unicast / multicast
+        self.mc_ring = int(getattr(self.ring_buf, "mc_ptr", 0) or 0)
+        if self.cfg.multicast == "on" and R > 1 and not self.mc_ring:
+            raise RuntimeError(f"multicast='on' but the rings could not be bound to a multicast object: "
+                               f"{getattr(self.ring_buf, 'mc_error', 'unsupported')}")
         flag_pages = [self.heap.peer_ptr(r, "flags") for r in range(R)]
         dev = lambda xs: torch.tensor(xs, dtype=torch.int64).to(self.device)  # noqa: E731
         self._push_tables = dev([self.heap.peer_ptr(r, "tables") for r in range(R)])
@@ -647,7 +681,7 @@ class DeviceEngine:
         d.d_tables, d.d_rings, d.d_flags = (self._push_tables.data_ptr(), self._push_rings.data_ptr(),
                                             self._push_flags.data_ptr())
         d.d_status = self._status_dev
-        d.max_polls = int(self.cfg.timeout_s * 2e6)
+        d.timeout_ns = int(self.cfg.timeout_s * 1e9)
         d.n_ranks, d.me, d.ctas_per_consumer = R, self.me, g.value
         d.owner_lo, d.owner_hi = self.me * self.P, (self.me + 1) * self.P
         self._push_desc = d
@@ -665,9 +699,21 @@ class DeviceEngine:
         d.ring_offset_bytes = ring_slot * self.B * self.ring_row
         d.ring_slot, d.window = ring_slot, k
         d.use, d.table_seq = self._use[ring_slot], table_seq
+        rep = self.specs[k].replicate
+        mc = rep and self.mc_ring != 0 and self._mc_ok(k)
+        d.table_rank = 0 if rep else -1          # replicated window: everybody receives instance 0's
+        d.d_mc_ring = self.mc_ring if mc else None
+        d.fills = self._fills[mc][ring_slot]
         self.plans[k].push_ptr(d, self.B, stream.cuda_stream)
+        self._fills[mc][ring_slot] += 1
         self._use[ring_slot] += 1
         self.launches += 1
+
+    def _mc_ok(self, k: int) -> bool:
+        """multimem.st moves whole 16-byte groups: fixed-size rows whose output is a multiple of 16 bytes."""
+        s = self.specs[k]
+        group_in = {N.CVT_COPY: 16, N.CVT_U8_BF16: 8, N.CVT_F32_BF16: 32, N.CVT_U8_F32: 4, N.CVT_I32_I64: 8}
+        return not s.var and s.sample_bytes % group_in[s.convert.mode] == 0
 
     def release_slot(self, ring_slot: int, stream) -> None:
         """Consumer side of the push form: tell every owner that `ring_slot` may be refilled."""

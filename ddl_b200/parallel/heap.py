@@ -79,6 +79,7 @@ class SymmetricHeap:
         self._host_dev: Dict[Tuple[int, str], int] = {}
         self._registered: List[int] = []
         self._attached: List[Tuple[int, int]] = []
+        self._vmm_imports: List[Tuple[int, int, int]] = []
         self._session = comm.bcast_obj(uuid.uuid4().hex[:12] if comm.rank == 0 else None, 0)
         self._closed = False
         if self.device.type == "cuda":
@@ -134,6 +135,72 @@ class SymmetricHeap:
         self.local[name] = buf
         return buf
 
+    def alloc_vmm(self, name: str, nbytes: int, multicast: bool = True) -> Buffer:
+        """Collective.  A buffer made with the virtual-memory-management API instead of cudaMalloc:
+        every rank creates physical memory of the same size, hands its POSIX file descriptor to all
+        peers (who map it: ``peer_ptr`` works as for IPC buffers), and -- where the platform has NVLS
+        multicast -- binds it to one multicast object; ``buf.mc_ptr`` is then an address through
+        which one ``multimem.st`` writes every rank's copy (0 when unavailable).  The reference's
+        windows are per instance (ddl/connection.py:88-139); this is what lets a batch ring be the
+        target of replicated delivery."""
+        from .multicast import _share_fd, query
+
+        if self.device.type != "cuda":
+            raise ValueError("VMM buffers live on CUDA devices")
+        lib, comm, dev = N.lib(), self.comm, self.device.index or 0
+        caps = comm.allgather_obj(query(self.device))
+        if not all(c["vmm"] and c["posix_fd"] for c in caps):
+            raise N.NativeError(-2, "VMM allocations with POSIX file-descriptor handles are not supported here")
+        use_mc = multicast and comm.size > 1 and all(c["multicast"] for c in caps)
+        gran = C.c_size_t(0)
+        if use_mc:
+            try:
+                N.check(lib.bddl_mc_granularity(int(nbytes), comm.size, C.byref(gran)))
+            except N.NativeError:
+                use_mc = False
+            use_mc = all(comm.allgather_obj(use_mc))
+        g = max(int(gran.value), 2 << 20)
+        size = (int(nbytes) + g - 1) // g * g
+        ptr, handle, fd, rounded = C.c_void_p(), C.c_uint64(), C.c_int32(), C.c_size_t()
+        N.check(lib.bddl_vmm_alloc(size, dev, g, C.byref(ptr), C.byref(handle), C.byref(fd), C.byref(rounded)))
+        size = int(rounded.value)
+        buf = Buffer(name, ptr.value, size, self.device, keep=("vmm", handle.value))
+        buf.mc_ptr = 0
+        buf.bytes().zero_()
+        torch.cuda.synchronize(self.device)
+        self.local[name] = buf
+        self.peers[(comm.rank, name)] = (ptr.value, size)
+        for root in range(comm.size):  # every rank's memory, mapped by every peer
+            got = _share_fd(comm, fd.value if comm.rank == root else None, root)
+            if comm.rank != root:
+                p, h = C.c_void_p(), C.c_uint64()
+                N.check(lib.bddl_vmm_import(got, size, dev, C.byref(p), C.byref(h)))
+                os.close(got)
+                self._vmm_imports.append((p.value, size, h.value))
+                self.peers[(root, name)] = (p.value, size)
+        os.close(fd.value)
+        if use_mc:
+            ok = True
+            try:
+                mc, mfd = C.c_uint64(), C.c_int32(-1)
+                if comm.rank == 0:
+                    N.check(lib.bddl_mc_create(size, comm.size, C.byref(mc), C.byref(mfd)))
+                my_fd = _share_fd(comm, mfd.value if comm.rank == 0 else None, 0)
+                if comm.rank != 0:
+                    N.check(lib.bddl_mc_import(my_fd, C.byref(mc)))
+                os.close(my_fd)
+                N.check(lib.bddl_mc_add_device(mc.value, dev))
+                comm.barrier()  # every device has joined before anyone binds memory
+                mc_ptr = C.c_void_p()
+                N.check(lib.bddl_mc_bind_and_map(mc.value, handle.value, size, dev, C.byref(mc_ptr)))
+                buf.mc_ptr, buf.mc_handle = int(mc_ptr.value), mc.value
+            except N.NativeError as e:
+                ok, buf.mc_error = False, str(e)
+            if not all(comm.allgather_obj(ok)):
+                buf.mc_ptr = 0  # one rank could not bind: everybody falls back to unicast stores
+        comm.barrier()
+        return buf
+
     def peer_dev_ptr(self, rank: int, name: str) -> int:
         """Device-visible address of a host-shared buffer (this process's mapping of it)."""
         return self._host_dev[(rank, name)]
@@ -145,7 +212,7 @@ class SymmetricHeap:
         mine = {}
         for name, b in self.local.items():
             if b._keep is not None:
-                continue  # pinned host staging is private
+                continue  # pinned host staging is private; VMM buffers were exchanged when they were made
             if getattr(b, "host_shared", False):
                 mine[name] = ("hshm", b.shm_name, b.nbytes, b.ptr, os.getpid(), -1)
                 self._host_dev[(self.comm.rank, name)] = b.dev_ptr
@@ -226,6 +293,8 @@ class SymmetricHeap:
             lib.bddl_ipc_close_handle(C.c_void_p(p))
         for p, n in self._attached:
             lib.bddl_shm_detach(C.c_void_p(p), n)
+        for p, n, h in self._vmm_imports:
+            lib.bddl_vmm_free(C.c_void_p(p), n, h)
         # freeing exported memory while a peer still holds it open is undefined (CUDA IPC): every
         # rank closes its imports first, then all meet, then each frees what it exported
         try:
@@ -236,6 +305,10 @@ class SymmetricHeap:
             b._u8 = None
             if b._keep is not None and b._keep[0] == "pinned":
                 lib.bddl_host_free(C.c_void_p(b.ptr))
+            elif b._keep is not None and b._keep[0] == "vmm":
+                if getattr(b, "mc_ptr", 0):
+                    lib.bddl_vmm_free(C.c_void_p(b.mc_ptr), b.nbytes, getattr(b, "mc_handle", 0))
+                lib.bddl_vmm_free(C.c_void_p(b.ptr), b.nbytes, b._keep[1])
             elif getattr(b, "host_shared", False):
                 if self.device.type == "cuda":
                     lib.bddl_host_unregister(C.c_void_p(b.ptr))

@@ -34,12 +34,13 @@ def query(device: torch.device) -> dict:
     return {"vmm": bool(v.value), "posix_fd": bool(f.value), "multicast": bool(m.value)}
 
 
-def _share_fd(comm: Comm, fd: Optional[int]) -> int:
-    """Rank 0 hands `fd` to every other rank; returns each rank's own descriptor."""
+def _share_fd(comm: Comm, fd: Optional[int], root: int = 0) -> int:
+    """Rank `root` hands `fd` to every other rank (SCM_RIGHTS over an abstract Unix socket);
+    returns each rank's own descriptor of the same object."""
     if comm.size == 1:
         return fd
-    name = comm.bcast_obj("\0bddl_fd_" + uuid.uuid4().hex[:12] if comm.rank == 0 else None, 0)
-    if comm.rank == 0:
+    name = comm.bcast_obj("\0bddl_fd_" + uuid.uuid4().hex[:12] if comm.rank == root else None, root)
+    if comm.rank == root:
         srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
         srv.bind(name)
         srv.listen(comm.size)

@@ -37,7 +37,11 @@ class DataProducerOnInitReturn:
     on the GPU (perm_gen) instead of calling ``execute_function``.  variable_length: rows are
     padded to nValues in the window, and after ``post_init`` the producer function exposes
     ``self.lengths`` (valid elements per row); only the valid part of a sample crosses NVLink and
-    the batch is padded with ``convert.pad_value`` while it is collated.
+    the batch is padded with ``convert.pad_value`` while it is collated.  replicate: every
+    consumer receives the batches of instance 0's window (a shared validation set, for example)
+    instead of its own: with ``exchange="push"`` each sample is converted once by the GPU that owns
+    it and written once through the NVLS multicast mapping of the batch rings (``multimem.st``;
+    NVSwitch replicates it), or once per consumer where multicast is unavailable.
     """
 
     nData: int
@@ -48,6 +52,7 @@ class DataProducerOnInitReturn:
     convert: Any = None
     shuffle_seed: Optional[int] = None
     variable_length: bool = False
+    replicate: bool = False
 
 
 @dataclasses.dataclass
@@ -73,3 +78,4 @@ class MetaData_Producer_To_Consumer:
     convert: Any = None
     shuffle_seed: Optional[int] = None
     variable_length: bool = False
+    replicate: bool = False

@@ -108,6 +108,9 @@ def timed_loop(loader, env, steps, warmup, e2e: bool, min_seconds: float, min_to
                     main.wait_stream(fs)
                 self.b.record(main)
                 torch.cuda.synchronize(dev)
+                eng = getattr(loader, "engine", None)
+                if eng is not None and hasattr(eng, "check_waits"):
+                    eng.check_waits()  # a bounded device-side wait that gave up raises here
             self.wall = time.perf_counter() - self.t0
             self.ms = self.a.elapsed_time(self.b) if cuda else self.wall * 1e3
             return False

@@ -61,7 +61,7 @@ int bddl_partner_select(bddl_rng_state* s, int32_t n_instance, int32_t my_rank, 
 /* ---- N2: perm_gen (replaces the in-place row shuffle rng.shuffle(my_ary), invoked at
  *      ddl/datapusher.py:154).  Shuffles n_tables slot tables of n entries each (table t starts
  *      at d_tables + t*table_stride) with the RNG states d_states[t], which are advanced in
- *      place on the device.  Bit-exact with bddl_host_shuffle_u64.  One CTA of 1024 threads per
+ *      place on the device.  Bit-exact with bddl_host_shuffle_u64.  One CTA of 512 threads per
  *      table: block-parallel draw generation and accept/reject, then the swaps applied in
  *      O(log n) rounds of deterministic reservations.  d_scratch: caller-owned device memory,
  *      n_tables * round_up(bddl_perm_gen_scratch_bytes(n), 64) bytes, 16-byte aligned. -------- */
@@ -141,6 +141,7 @@ int bddl_gather_step(const bddl_gather_desc* desc, void* stream, void* wait_even
 #define BDDL_FLAG_BARRIER0 0      /* [rank]              flag barrier slots                          */
 #define BDDL_FLAG_READY0 256      /* [slot]              += 1 by every owner per fill of my slot     */
 #define BDDL_FLAG_STOP 272        /*                     non-zero cancels every wait                 */
+#define BDDL_FLAG_DONE_MC0 288    /* [slot]              local CTA tickets of multicast launches     */
 #define BDDL_FLAG_FREE0 512       /* [slot][consumer]    = fills consumed, stored by that consumer   */
 #define BDDL_FLAG_DONE0 1536      /* [slot][consumer]    local CTA tickets of the push kernel        */
 #define BDDL_FLAG_TABLE0 2560     /* [window][consumer]  = tables produced, stored by that consumer  */
@@ -150,7 +151,7 @@ typedef struct bddl_push_desc {
     uint32_t* const* d_flags;     /* device array [n_ranks]: every rank's flag page                  */
     int64_t table_offset_bytes;   /* where this step's slice starts inside a table buffer            */
     int64_t ring_offset_bytes;    /* where the ring slot starts inside a ring                        */
-    uint64_t max_polls;           /* bound of every in-kernel wait (0 = unbounded)                   */
+    uint64_t timeout_ns;          /* bound of every in-kernel wait, in nanoseconds (0 = unbounded)   */
     uint32_t* d_status;
     int32_t n_ranks, me;
     int32_t ring_slot, window;
@@ -158,6 +159,12 @@ typedef struct bddl_push_desc {
     int32_t ctas_per_consumer;    /* from bddl_push_ctas_per_consumer; the same on every launch      */
     uint32_t use;                 /* how often this ring slot has been filled before                 */
     uint32_t table_seq;           /* the consumers' `table` words must have reached this value       */
+    /* replicated windows (K9/N6 multicast_put fused with the N5 epilogues): every consumer receives
+     * rank `table_rank`'s window; with d_mc_ring (the NVLS multicast mapping of the rings) each sample
+     * is stored once with multimem.st and replicated by NVSwitch, otherwise once per consumer. */
+    void* d_mc_ring;              /* or NULL                                                         */
+    int32_t table_rank;           /* -1: every consumer receives its own window                      */
+    uint32_t fills;               /* earlier launches of this kind (unicast / multicast) into the slot */
 } bddl_push_desc;
 int bddl_push_ctas_per_consumer(int32_t n_ranks, int32_t max_ctas, int32_t* out);
 int bddl_exchange_push_collate(const bddl_gather_desc* desc, const bddl_push_desc* push, void* stream);
@@ -194,6 +201,8 @@ int bddl_malloc(void** p, size_t bytes);
 int bddl_free(void* p);
 int bddl_memset_async(void* p, int value, size_t bytes, void* stream);
 int bddl_memcpy_async(void* dst, const void* src, size_t bytes, int32_t kind, void* stream);
+int bddl_memcpy2d_async(void* dst, size_t dst_pitch, const void* src, size_t src_pitch, size_t width_bytes,
+                        size_t rows, int32_t kind, void* stream);
 int bddl_stream_synchronize(void* stream);
 int bddl_event_create(void** ev);               /* cudaEventDisableTiming */
 int bddl_event_destroy(void* ev);
@@ -258,11 +267,12 @@ int bddl_stream_wait_value32(void* stream, uint32_t* d_addr, uint32_t value);   
 int bddl_stream_write_value32(void* stream, uint32_t* d_addr, uint32_t value);
 /* Store (add=0) or add (add=1) `value` to n counters (device array of addresses, peers allowed). */
 int bddl_flag_signal(uint32_t* const* d_targets, int32_t n, uint32_t value, int32_t add, void* stream);
-/* Bounded in-kernel wait; *d_status: 0 satisfied, 1 timed out, 2 stopped. */
-int bddl_flag_wait(const uint32_t* d_flag, uint32_t value, uint64_t max_polls, const uint32_t* d_stop,
+/* Bounded in-kernel wait (timeout in nanoseconds of the GPU's global timer, 0 = unbounded);
+ * *d_status (device or mapped host memory): 0 satisfied, 1 timed out, 2 stopped. */
+int bddl_flag_wait(const uint32_t* d_flag, uint32_t value, uint64_t timeout_ns, const uint32_t* d_stop,
                    uint32_t* d_status, void* stream);
 /* All-ranks barrier over per-rank flag pages (d_pages[r] = rank r's page, n_ranks words each). */
-int bddl_flag_barrier(uint32_t* const* d_pages, int32_t n_ranks, int32_t me, uint32_t epoch, uint64_t max_polls,
+int bddl_flag_barrier(uint32_t* const* d_pages, int32_t n_ranks, int32_t me, uint32_t epoch, uint64_t timeout_ns,
                       const uint32_t* d_stop, uint32_t* d_status, void* stream);
 
 /* Host side: POSIX shared-memory windows and flag words for producer processes. */

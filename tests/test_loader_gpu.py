@@ -87,6 +87,12 @@ def test_integrity_mode_cross_checks_kernel_forms():
     _run(ddl.LoaderConfig(verify=True, ring_depth=3, prefetch_depth=2), v=64)
 
 
+def test_canary_mode_on_gpu():
+    """(lend, batch) stamps written behind every assembly by cuStreamWriteValue32 and checked on hand-out and mark."""
+    _run(ddl.LoaderConfig(canary=True, ring_depth=3, prefetch_depth=2))
+    _run(ddl.LoaderConfig(canary=True, residency="host", host_stage="pull"), v=16)
+
+
 def test_tracing_reports_device_time_per_stage():
     got = {}
 
@@ -248,6 +254,23 @@ def test_multi_gpu_u8_to_bf16_with_integrity_mode(tmp_path, nproc, exchange):
            "ring_depth": 3, "prefetch_depth": 2, "timeout_s": 60.0}
     _torchrun(nproc, cfg, tmp_path)
     _check_order(tmp_path, nproc, 1, 2048, 128, 4, 0.5)
+
+
+@pytest.mark.multigpu
+@pytest.mark.parametrize("nproc,multicast", [(2, "auto"), (2, "off"), (8, "auto")])
+def test_replicated_window_delivered_to_every_consumer(tmp_path, nproc, multicast):
+    """replicate=True: every consumer receives instance 0's window.  Each sample is converted once by
+    the GPU that owns it and stored once through the NVLS multicast mapping of the batch rings
+    (multimem.st inside the push kernel) -- or once per consumer with multicast='off'; both must
+    deliver exactly what the unicast oracle prescribes for instance 0."""
+    _need_gpus(nproc)
+    cfg = {"n_instances": nproc, "n_producers": 2, "n": 4096, "v": 32, "B": 256, "epochs": 6, "fraction": 0.5,
+           "shuffle_mode": "device", "declare_seed": True, "cpu": False, "exchange": "push", "timeout_s": 60.0,
+           "ring_depth": 4, "prefetch_depth": 2, "fetch_streams": 2, "replicate": True, "multicast": multicast}
+    _torchrun(nproc, cfg, tmp_path)
+    exp = expected_epochs(nproc, 2, 4096, 256, 6, 0.5)[0]
+    for i in range(nproc):
+        assert np.array_equal(np.load(os.path.join(str(tmp_path), f"seen_{i}.npy")), exp), f"consumer {i}"
 
 
 @pytest.mark.multigpu

@@ -48,7 +48,8 @@ class IdProducer(ddl.ProducerFunctionSkeleton):
         self.rng = np.random.default_rng(seed=self.rank_global)
         cv = ddl.Convert.cast_f32_bf16() if CFG.get("convert") else None
         return ddl.DataProducerOnInitReturn(self.n, self.v, (self.n, self.v), (1, self.v - 1), convert=cv,
-                                            shuffle_seed=self.rank_global if self.declare_seed else None)
+                                            shuffle_seed=self.rank_global if self.declare_seed else None,
+                                            replicate=bool(CFG.get("replicate")))
 
     def post_init(self, **kw):
         self.my_ary = kw["my_ary"]
@@ -138,7 +139,7 @@ if __name__ == "__main__":
                                     timeout_s=CFG.get("timeout_s", 120.0), verify=CFG.get("verify"),
                                     exchange=CFG.get("exchange"), barrier=CFG.get("barrier"),
                                     ring_depth=CFG.get("ring_depth"), prefetch_depth=CFG.get("prefetch_depth"),
-                                    fetch_streams=CFG.get("fetch_streams"))
+                                    fetch_streams=CFG.get("fetch_streams"), multicast=CFG.get("multicast"))
     main = ddl.distributed_dataloader(body, n_instances=CFG["n_instances"], n_producers=CFG.get("n_producers"),
                                       config=cfg, device="cpu" if CFG.get("cpu", True) else None,
                                       n_storage=CFG.get("n_storage", 0))
