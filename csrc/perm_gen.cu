@@ -5,28 +5,33 @@
 // Rows never move here: the permutation is applied to a table of 64-bit slot ids.
 //
 // numpy's shuffle is "for i = n-1 .. 1: j = bounded_draw(i); swap(t[i], t[j])" with masked
-// rejection on a stream of 32-bit draws -- sequential as written.  One CTA of
-// 512 threads per table runs it in two parallel phases that give the same result bit for bit:
+// rejection on a stream of 32-bit draws -- sequential as written.  One thread-block
+// cluster (8 CTAs x 512 threads) per table runs it in two parallel phases that give the same
+// result bit for bit:
 //
-//   A. targets.  PCG64 is an LCG, so thread t jumps straight to output t of the current batch
-//      (1024 draws per batch).  Whether draw k is accepted depends only on how many earlier draws
-//      of the batch were (that fixes the index it is drawn for, hence the mask and the bound), so
-//      accept/reject of the whole batch is the unique fixed point of "scan the accept bits,
-//      re-evaluate" -- a few block-wide scans (2-6 rounds; more only in the last few thousand
-//      entries).  Accepted draws are written as J[i] = j: the target of the swap for index i.
-//      The batch in which the table ends leaves the generator exactly where numpy would (number
-//      of outputs consumed, buffered upper half).
-//   B. swaps.  Step i touches positions i and J[i]; steps commute unless they share a position.
-//      Deterministic reservations: every pending step writes its priority (earlier step = larger
-//      i) to both of its positions with a 64-bit atomicMax tagged by the round number; a step that
-//      holds both positions has no pending predecessor and swaps; the rest retry.  The dependence
-//      depth of a random Fisher-Yates is O(log n): 33 / 35 / 49 rounds and 3.5 n step attempts in
-//      total for 16 k / 100 k / 1 M entries.
+//   A. targets (CTA 0 of the cluster; the others clear the reservation words meanwhile).  PCG64 is
+//      an LCG, so thread t jumps straight to its two outputs of the current batch (2048 draws per
+//      batch).  Whether draw k is accepted depends only on how many earlier draws of the batch
+//      were (that fixes the index it is drawn for, hence the mask and the bound), so accept/reject
+//      of the whole batch is the unique fixed point of "scan the accept bits, re-evaluate": one
+//      block-wide scan and ONE barrier per round (double-buffered warp sums, the "nothing
+//      changed" flag is read behind the next round's barrier), 3-6 rounds, more only in the last
+//      few thousand entries.  Accepted draws are written as J[i] = j: the target of the swap for
+//      index i.  The batch in which the table ends leaves the generator exactly where numpy would
+//      (number of outputs consumed, buffered upper half).
+//   B. swaps (the whole cluster).  Step i touches positions i and J[i]; steps commute unless they
+//      share a position.  Deterministic reservations: every pending step writes its priority
+//      (earlier step = larger i) to both of its positions with a 64-bit atomicMax tagged by the
+//      round number; a step that holds both positions has no pending predecessor and swaps; the
+//      rest retry.  The dependence depth of a random Fisher-Yates is O(log n): 33 / 35 / 49 rounds
+//      and 3.5 n step attempts in total for 16 k / 100 k / 1 M entries; a round is two cluster
+//      barriers and two levels of L2 latency.
 //
-// Scratch (caller-owned, bddl_perm_gen_scratch_bytes): J, the reservation words and two work
-// lists; everything else lives in registers and 200 bytes of shared memory, so the kernel
-// co-resides with the batch-assembly kernel on one SM and runs one iteration ahead on a side
-// stream.
+// Scratch (caller-owned, bddl_perm_gen_scratch_bytes): J, the reservation words, two work lists
+// and two counters; everything else lives in registers and 300 bytes of shared memory, so the
+// CTAs co-reside with the batch-assembly kernel and the shuffle runs one iteration ahead on a
+// high-priority side stream.
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 
 #include "../include/ddl_b200.h"
@@ -34,20 +39,25 @@
 #include "launch_count.h"
 #include "rng_pcg64.h"
 
+namespace cg = cooperative_groups;
+
 namespace {
 
 constexpr int kThreads = 512;  // + <= 64 registers: co-resides with a 512-thread batch-assembly CTA on one SM
 constexpr int kWarps = kThreads / 32;
+constexpr int kCluster = 8;
+constexpr int kDraws = 4;  // per thread and batch: two 64-bit outputs
 
 struct Ctl {
-    uint32_t warp_sum[kWarps];
+    uint32_t warp_sum[2][kWarps];
+    uint32_t changed[2];
     uint32_t end_thread;  // thread whose draw completed the table
-    uint32_t end_half;    // 0: its low half was the last draw consumed, 1: its high half
-    uint32_t count[2];    // work-list lengths (ping-pong)
+    uint32_t end_draw;    // which of its four draws
 };
 
-// Exclusive scan of `x` over the CTA; *total = sum over all threads.  Two barriers.
-__device__ __forceinline__ uint32_t block_excl_scan(uint32_t x, Ctl& c, uint32_t* total) {
+// Exclusive scan of `x` over the CTA through buffer `par` (callers alternate it); *total = sum over
+// all threads.  One barrier.
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t x, Ctl& c, int par, uint32_t* total) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t incl = x;
 #pragma unroll
@@ -55,10 +65,9 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t x, Ctl& c, uint32_t
         const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
         if (lane >= o) incl += y;
     }
-    __syncthreads();  // the previous scan's warp_sum has been read by everyone
-    if (lane == 31) c.warp_sum[warp] = incl;
+    if (lane == 31) c.warp_sum[par][warp] = incl;
     __syncthreads();
-    uint32_t w = lane < kWarps ? c.warp_sum[lane] : 0u;
+    uint32_t w = lane < kWarps ? c.warp_sum[par][lane] : 0u;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const uint32_t y = __shfl_up_sync(0xffffffffu, w, o);
@@ -69,30 +78,18 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t x, Ctl& c, uint32_t
     return before + incl - x;
 }
 
-__global__ void __launch_bounds__(kThreads) perm_gen_kernel(uint64_t* tables, int64_t table_stride, int64_t n,
-                                                            BddlRng* states, uint8_t* scratch, int64_t scratch_stride) {
-    __shared__ Ctl ctl;
+// Phase A, one CTA: J[i] = swap target of index i for i = n-1 .. 1; advances *gst like numpy.
+__device__ void draw_targets(Ctl& ctl, uint32_t* __restrict__ J, int64_t n, BddlRng* gst) {
     const int tid = threadIdx.x;
-    uint64_t* const tbl = tables + (int64_t)blockIdx.x * table_stride;
-    BddlRng* const gst = states + blockIdx.x;
-    uint8_t* const my = scratch + (int64_t)blockIdx.x * scratch_stride;
-    const int64_t n_pad = (n + 1) & ~1LL;
-    unsigned long long* const R = reinterpret_cast<unsigned long long*>(my);  // [n] round << 32 | priority
-    uint32_t* const J = reinterpret_cast<uint32_t*>(R + n);                   // [n] swap target of index i
-    uint32_t* list[2] = {J + n_pad, J + 2 * n_pad};                           // pending steps (ping-pong)
-
-    // CTA-uniform copy of the generator
-    const U128 base = {gst->state_lo, gst->state_hi};
+    const U128 base = {gst->state_lo, gst->state_hi};  // CTA-uniform copy of the generator
     const U128 inc = {gst->inc_lo, gst->inc_hi};
     uint32_t has32 = gst->has_uint32;
-    uint32_t pending = gst->uinteger;
+    const uint32_t pending = gst->uinteger;
     uint64_t draws = gst->draws32;
     int64_t i = n - 1;
+    if (tid < 2) ctl.changed[tid] = 0;
+    __syncthreads();  // every thread has read the generator before the finishing thread rewrites it
 
-    for (int64_t x = tid; x < n; x += kThreads) R[x] = 0ULL;
-    if (tid < 2) ctl.count[tid] = 0;
-
-    // ---- phase A: J[i] for i = n-1 .. 1 ----------------------------------------------------
     if (has32 && i >= 1) {  // a buffered upper half from an earlier call is the first draw
         const uint64_t v = (uint64_t)pending & bddl_mask_for((uint64_t)i);
         has32 = 0;
@@ -102,102 +99,161 @@ __global__ void __launch_bounds__(kThreads) perm_gen_kernel(uint64_t* tables, in
             --i;
         }
     }
-    if (i >= 1) {
-        U128 jm, jp, lm, lp;
-        pcg_jump_coeffs(inc, (uint64_t)kThreads, &jm, &jp);    // one batch ahead
-        pcg_jump_coeffs(inc, (uint64_t)(tid + 1), &lm, &lp);   // thread t owns output t+1 after `base`
-        U128 st = u128_add(u128_mul(lm, base), lp);
-        for (;;) {
-            const uint64_t out = pcg_output(st);
-            const uint32_t d0 = (uint32_t)out, d1 = (uint32_t)(out >> 32);  // numpy hands out the low half first
-            uint32_t a0 = 0, a1 = 0, excl = 0, total = 0;
-            uint64_t v0 = 0, v1 = 0;
-            int64_t i0 = 0, i1 = 0;
-            for (;;) {
-                excl = block_excl_scan(a0 + a1, ctl, &total);
-                i0 = i - (int64_t)excl;
-                i1 = i0 - (int64_t)a0;
-                v0 = i0 >= 1 ? ((uint64_t)d0 & bddl_mask_for((uint64_t)i0)) : 0;
-                v1 = i1 >= 1 ? ((uint64_t)d1 & bddl_mask_for((uint64_t)i1)) : 0;
-                const uint32_t n0 = i0 >= 1 && v0 <= (uint64_t)i0;
-                const uint32_t n1 = i1 >= 1 && v1 <= (uint64_t)i1;
-                const int changed = (n0 != a0) | (n1 != a1);
-                a0 = n0;
-                a1 = n1;
-                if (!__syncthreads_or(changed)) break;  // fixed point: (a, idx, v) are numpy's
-            }
-            if (a0) J[i0] = (uint32_t)v0;
-            if (a1) J[i1] = (uint32_t)v1;
-            if ((int64_t)total >= i) {
-                // the table ends inside this batch: the draw that was accepted for index 1 is the
-                // last one consumed; leave the generator exactly where numpy would
-                if (a0 && i0 == 1) {
-                    ctl.end_thread = tid;
-                    ctl.end_half = 0;
-                } else if (a1 && i1 == 1) {
-                    ctl.end_thread = tid;
-                    ctl.end_half = 1;
-                }
-                __syncthreads();
-                const uint32_t et = ctl.end_thread, eh = ctl.end_half;
-                if (tid == (int)et) {
-                    gst->state_lo = st.lo;
-                    gst->state_hi = st.hi;
-                    gst->has_uint32 = eh == 0 ? 1u : 0u;  // low half used, high half buffered
-                    gst->uinteger = eh == 0 ? d1 : pending;
-                    gst->draws32 = draws + 2ULL * et + eh + 1ULL;
-                }
-                i = 0;
-                break;
-            }
-            i -= (int64_t)total;
-            draws += 2ULL * kThreads;
-            st = u128_add(u128_mul(jm, st), jp);
+    if (i < 1) {  // nothing drawn from fresh outputs: only the buffered half may have been used up
+        if (tid == 0) {
+            gst->has_uint32 = has32;
+            gst->draws32 = draws;
         }
-    } else if (tid == 0) {
-        // nothing drawn from fresh outputs: only the buffered half may have been used up
-        gst->has_uint32 = has32;
-        gst->draws32 = draws;
+        return;
     }
-    __syncthreads();  // J and the zeroed reservation words are complete
+    U128 jm, jp, lm, lp;
+    pcg_jump_coeffs(inc, (uint64_t)(2 * kThreads), &jm, &jp);  // one batch ahead
+    pcg_jump_coeffs(inc, (uint64_t)(2 * tid + 1), &lm, &lp);   // thread t owns outputs 2t+1 and 2t+2 after `base`
+    U128 st0 = u128_add(u128_mul(lm, base), lp);
+    U128 st1 = pcg_step(st0, inc);
+    uint32_t rr = 0;  // scans so far: alternates the scan / flag buffers, also across batches
+    for (;;) {
+        const uint64_t o0 = pcg_output(st0), o1 = pcg_output(st1);
+        // numpy hands out the low half of an output first
+        const uint32_t d[kDraws] = {(uint32_t)o0, (uint32_t)(o0 >> 32), (uint32_t)o1, (uint32_t)(o1 >> 32)};
+        uint32_t a[kDraws] = {0, 0, 0, 0};  // accept bits
+        int64_t idx[kDraws] = {0, 0, 0, 0};
+        uint32_t v[kDraws] = {0, 0, 0, 0};
+        uint32_t total = 0;
+        for (uint32_t r = 0;; ++r, ++rr) {
+            const uint32_t excl = block_excl_scan(a[0] + a[1] + a[2] + a[3], ctl, (int)(rr & 1u), &total);
+            // did the previous evaluation change anything anywhere?  It stamped its flag with its
+            // round number + 1 if so; a flag left from two rounds ago carries an older stamp.
+            if (r > 0 && ctl.changed[(rr - 1u) & 1u] != rr)
+                break;  // fixed point: (a, idx, v) are numpy's, `total` counts the accepted draws
+            int64_t run = i - (int64_t)excl;
+            uint32_t changed = 0;
+#pragma unroll
+            for (int k = 0; k < kDraws; ++k) {
+                idx[k] = run;
+                const bool live = run >= 1;
+                const uint64_t m = live ? ((uint64_t)d[k] & bddl_mask_for((uint64_t)run)) : 0ULL;
+                const uint32_t nk = live && m <= (uint64_t)run;
+                v[k] = (uint32_t)m;
+                changed |= nk ^ a[k];
+                a[k] = nk;
+                run -= (int64_t)nk;  // later draws of this thread already see the new bit
+            }
+            if (changed) ctl.changed[rr & 1u] = rr + 1u;
+        }
+#pragma unroll
+        for (int k = 0; k < kDraws; ++k)
+            if (a[k]) J[idx[k]] = v[k];
+        if ((int64_t)total >= i) {
+            // the table ends inside this batch: the draw accepted for index 1 is the last one
+            // consumed; leave the generator exactly where numpy would
+#pragma unroll
+            for (int k = 0; k < kDraws; ++k)
+                if (a[k] && idx[k] == 1) {
+                    ctl.end_thread = tid;
+                    ctl.end_draw = k;
+                }
+            __syncthreads();
+            const uint32_t et = ctl.end_thread, ek = ctl.end_draw;
+            if (tid == (int)et) {
+                const U128 fin = ek < 2 ? st0 : st1;
+                gst->state_lo = fin.lo;
+                gst->state_hi = fin.hi;
+                gst->has_uint32 = (ek & 1u) ? 0u : 1u;  // low half used last: its high half is buffered
+                gst->uinteger = (ek & 1u) ? pending : d[ek + 1 < kDraws ? ek + 1 : ek];
+                gst->draws32 = draws + (uint64_t)kDraws * et + ek + 1ULL;
+            }
+            return;
+        }
+        i -= (int64_t)total;
+        draws += (uint64_t)kDraws * kThreads;
+        st0 = u128_add(u128_mul(jm, st0), jp);
+        st1 = u128_add(u128_mul(jm, st1), jp);
+    }
+}
 
-    // ---- phase B: apply the swaps --------------------------------------------------------------
+struct Hdr {
+    uint32_t count[2];  // lengths of the two work lists
+};
+
+__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kThreads)
+    perm_gen_kernel(uint64_t* tables, int64_t table_stride, int64_t n, BddlRng* states, uint8_t* scratch,
+                    int64_t scratch_stride) {
+    __shared__ Ctl ctl;
+    cg::cluster_group cluster = cg::this_cluster();
+    const int tid = threadIdx.x;
+    const int crank = (int)cluster.block_rank();
+    const int table = blockIdx.x / kCluster;
+    const uint32_t gtid = (uint32_t)crank * kThreads + tid;
+    constexpr uint32_t gthreads = kCluster * kThreads;
+    uint64_t* const tbl = tables + (int64_t)table * table_stride;
+    uint8_t* const my = scratch + (int64_t)table * scratch_stride;
+    Hdr* const hdr = reinterpret_cast<Hdr*>(my);
+    unsigned long long* const R = reinterpret_cast<unsigned long long*>(my + 64);  // [n] round << 32 | priority
+    unsigned long long* const list0 = R + n;                                       // pending steps: j << 32 | i
+    unsigned long long* const list1 = list0 + n;
+    uint32_t* const J = reinterpret_cast<uint32_t*>(list1 + n);                    // [n_pad] swap target of index i
+
+    if (crank == 0) {
+        draw_targets(ctl, J, n, states + table);
+    } else {
+        for (int64_t x = (int64_t)gtid - kThreads; x < n; x += gthreads - kThreads) R[x] = 0ULL;
+        if (gtid == kThreads) hdr->count[0] = hdr->count[1] = 0;
+    }
+    if (kCluster == 1) {
+        for (int64_t x = tid; x < n; x += kThreads) R[x] = 0ULL;
+        if (tid == 0) hdr->count[0] = hdr->count[1] = 0;
+    }
+    __threadfence();
+    cluster.sync();  // J, the cleared reservation words and the counters are visible to the cluster
+
+    // ---- phase B: apply the swaps ----------------------------------------------------------------
     // pending steps: every i with J[i] != i (a step that swaps an entry with itself is a no-op)
-    for (int64_t b = 1; b < n; b += kThreads) {
-        const int64_t x = b + tid;
-        const bool live = x < n && J[x] != (uint32_t)x;
+    for (int64_t b = 1; b < n; b += gthreads) {
+        const int64_t x = b + gtid;
+        uint32_t j = 0;
+        bool live = false;
+        if (x < n) {
+            j = __ldcg(J + x);
+            live = j != (uint32_t)x;
+        }
         const unsigned m = __ballot_sync(0xffffffffu, live);
         uint32_t pos = 0;
-        if ((tid & 31) == 0 && m) pos = atomicAdd(&ctl.count[0], (uint32_t)__popc(m));
+        if ((tid & 31) == 0 && m) pos = atomicAdd(&hdr->count[0], (uint32_t)__popc(m));
         pos = __shfl_sync(0xffffffffu, pos, 0);
-        if (live) list[0][pos + __popc(m & ((1u << (tid & 31)) - 1u))] = (uint32_t)x;
+        if (live) __stcg(list0 + pos + __popc(m & ((1u << (tid & 31)) - 1u)), ((unsigned long long)j << 32) | (uint32_t)x);
     }
-    __syncthreads();
+    __threadfence();
+    cluster.sync();
     int cur = 0;
     for (unsigned long long round = 1;; ++round) {
-        const uint32_t cnt = ctl.count[cur];
+        const uint32_t cnt = __ldcg(&hdr->count[cur]);
         if (cnt == 0) break;
-        const uint32_t* in = list[cur];
-        uint32_t* outl = list[cur ^ 1];
+        const unsigned long long* in = cur ? list1 : list0;
+        unsigned long long* outl = cur ? list0 : list1;
         const unsigned long long tag = round << 32;
-        if (tid == 0) ctl.count[cur ^ 1] = 0;
-        for (uint32_t q = tid; q < cnt; q += kThreads) {  // reserve both positions
-            const uint32_t x = __ldcg(in + q);
-            const uint32_t j = __ldcg(J + x);
+        // the other counter was last read at the top of the previous round (two barriers ago)
+        if (gtid == 0) hdr->count[cur ^ 1] = 0;
+        for (uint32_t q = gtid; q < cnt; q += gthreads) {  // reserve both positions
+            const unsigned long long e = __ldcg(in + q);
+            const uint32_t x = (uint32_t)e, j = (uint32_t)(e >> 32);
             atomicMax(R + x, tag | x);
             atomicMax(R + j, tag | x);
         }
-        __syncthreads();
-        for (uint32_t q0 = 0; q0 < cnt; q0 += kThreads) {  // commit or retry (warp-uniform trip count)
-            const uint32_t q = q0 + tid;
+        __threadfence();
+        cluster.sync();
+        for (uint32_t q0 = 0; q0 < cnt; q0 += gthreads) {  // commit or retry (warp-uniform trip count)
+            const uint32_t q = q0 + gtid;
             bool retry = false;
-            uint32_t x = 0;
+            unsigned long long e = 0;
             if (q < cnt) {
-                x = __ldcg(in + q);
-                const uint32_t j = __ldcg(J + x);
+                e = __ldcg(in + q);
+                const uint32_t x = (uint32_t)e, j = (uint32_t)(e >> 32);
                 const unsigned long long want = tag | x;
-                if (__ldcg(R + x) == want && __ldcg(R + j) == want) {
-                    const uint64_t a = __ldcg(tbl + x), b = __ldcg(tbl + j);
+                // the four loads are independent: one level of L2 latency for the whole decision
+                const unsigned long long rx = __ldcg(R + x), rj = __ldcg(R + j);
+                const uint64_t a = __ldcg(tbl + x), b = __ldcg(tbl + j);
+                if (rx == want && rj == want) {
                     __stcg(tbl + x, b);
                     __stcg(tbl + j, a);
                 } else {
@@ -206,11 +262,12 @@ __global__ void __launch_bounds__(kThreads) perm_gen_kernel(uint64_t* tables, in
             }
             const unsigned m = __ballot_sync(0xffffffffu, retry);
             uint32_t pos = 0;
-            if ((tid & 31) == 0 && m) pos = atomicAdd(&ctl.count[cur ^ 1], (uint32_t)__popc(m));
+            if ((tid & 31) == 0 && m) pos = atomicAdd(&hdr->count[cur ^ 1], (uint32_t)__popc(m));
             pos = __shfl_sync(0xffffffffu, pos, 0);
-            if (retry) __stcg(outl + pos + __popc(m & ((1u << (tid & 31)) - 1u)), x);
+            if (retry) __stcg(outl + pos + __popc(m & ((1u << (tid & 31)) - 1u)), e);
         }
-        __syncthreads();
+        __threadfence();
+        cluster.sync();
         cur ^= 1;
     }
 }
@@ -220,7 +277,7 @@ __global__ void __launch_bounds__(kThreads) perm_gen_kernel(uint64_t* tables, in
 extern "C" int64_t bddl_perm_gen_scratch_bytes(int64_t n) {
     if (n < 0) return 0;
     const int64_t n_pad = (n + 1) & ~1LL;
-    return n * 8 + 3 * n_pad * 4 + 64;  // reservations, targets, two work lists
+    return 64 + n * 8 * 3 + n_pad * 4;  // counters, reservation words, two work lists, targets
 }
 
 extern "C" int bddl_perm_gen(uint64_t* d_tables, int64_t table_stride, int64_t n, bddl_rng_state* d_states,
@@ -233,8 +290,8 @@ extern "C" int bddl_perm_gen(uint64_t* d_tables, int64_t table_stride, int64_t n
     if (!d_scratch || ((uintptr_t)d_scratch & 15) || scratch_bytes < per_table * n_tables)
         return bddl_fail(BDDL_ERR_INVALID, "perm_gen: scratch of %lld bytes needed (16-byte aligned), got %lld",
                          (long long)(per_table * n_tables), (long long)scratch_bytes);
-    perm_gen_kernel<<<n_tables, kThreads, 0, (cudaStream_t)stream>>>(d_tables, table_stride, n, (BddlRng*)d_states,
-                                                                      (uint8_t*)d_scratch, per_table);
+    perm_gen_kernel<<<n_tables * kCluster, kThreads, 0, (cudaStream_t)stream>>>(
+        d_tables, table_stride, n, (BddlRng*)d_states, (uint8_t*)d_scratch, per_table);
     bddl_count_launch(1);
     BDDL_CUDA(cudaGetLastError());
     return 0;

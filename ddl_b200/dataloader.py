@@ -411,7 +411,7 @@ class DistributedDataLoader(DistributedDataloaderABC):
             ts = self._train_stream()
             ev.record(ts)  # the "free" flag of this ring slot, in stream-event form
             if self.engine is not None and self.engine.push:
-                self.engine.release_slot(self._cur_slot, ts)
+                self.engine.release_slot(self._cur_slot, ev)
         self.batch += 1
         if self.batch % self.batches_per_window[self.target_rank - 1] == 0:
             self._window_done = True  # every batch of this epoch's window was delivered
@@ -551,20 +551,47 @@ class DistributedDataLoader(DistributedDataloaderABC):
 
     # -- checkpoint (absent in the reference) ---------------------------------------------------
     def state_dict(self) -> dict:
-        """Everything needed to continue the exact sample sequence: position, slot tables, RNG
-        streams, partner-RNG streams.  Cheap because rows never move: a table is 8 bytes per
-        sample.  Take it between batches (after ``mark(END_OF_BATCH)``), at the same step on
-        every rank."""
+        """Everything needed to continue the exact sample sequence.  Take it between batches
+        (after ``mark(END_OF_BATCH)``), at the same step on every rank.
+
+        device transport: position, slot tables, RNG streams, partner-RNG streams -- cheap because
+        rows never move (a table is 8 bytes per sample).  process transport: the position only; the
+        windows and generators are state of the producer processes, which are deterministic
+        functions of their seeds, so ``load_state_dict`` replays the hand-overs instead."""
         if self.transport != "device":
-            raise NotImplementedError("checkpoints cover the device transport; host windows are user state")
+            return {"transport": "process", "epoch": self.epoch, "batch": self.batch, "target_rank": self.target_rank,
+                    "window_done": getattr(self, "_window_done", False)}
         return {"epoch": self.epoch, "batch": self.batch, "target_rank": self.target_rank, "len": self._len,
                 "window_done": getattr(self, "_window_done", False),
                 "producers": [p.state_dict() for p in self.connection.pushers]}
 
+    def _replay_to(self, d: dict) -> None:
+        """Process transport: bring a freshly constructed loader (and, through the ordinary lend /
+        return tokens, its producer processes) to the checkpointed position.  Every skipped epoch
+        borrows its window and hands it straight back, so each producer runs exactly the exchanges
+        and shuffles it ran before the checkpoint; no batch is fetched."""
+        if self.epoch != 0 or self.batch != 0:
+            raise RuntimeError("process-transport checkpoints are loaded into a freshly constructed loader")
+        self._pref = {}
+        windows = d["epoch"] + (1 if d.get("window_done") else 0)
+        for _ in range(windows):
+            if self.cuda:
+                for fs in self.fetch_streams:
+                    fs.synchronize()  # prefetches of the window being skipped
+            self._end_access_epoch()
+            self._advance_to_next_producer()
+            self._start_access_epoch()
+        self.epoch, self.batch = d["epoch"], d["batch"]
+        self._window_done = d.get("window_done", False)
+        self._iter_start = self._len if self._window_done else self.batch
+        for i in range(self.cfg.prefetch_depth):
+            self._prefetch(self._iter_start + i)
+
     def load_state_dict(self, d: dict) -> None:
         """Resume on a freshly constructed loader (same producer function, batch size, world)."""
         if self.transport != "device":
-            raise NotImplementedError("checkpoints cover the device transport")
+            self._replay_to(d)
+            return
         for p, pd in zip(self.connection.pushers, d["producers"]):
             p.load_state_dict(pd)
         self.epoch, self.batch, self.target_rank, self._len = d["epoch"], d["batch"], d["target_rank"], d["len"]

@@ -275,10 +275,12 @@ class DevicePusher:
                               rank_global=self.rank_global, my_ary=self.my_ary, n_instance=self.n_instance)
             engine.load_shard(k, self.my_ary)
         if engine.specs[k].var:
-            lens = getattr(self.producer_function, "lengths", None)
-            if self.remote or lens is None:
-                raise ValueError("variable_length windows need producer_function.lengths after post_init "
-                                 "(and are not supported on dedicated storage GPUs yet)")
+            if self.remote:  # post_init ran on the storage rank, which reports the row lengths
+                lens = self.env.comm_global.recv_obj(self.env.storage_rank_of(self.env.color), tag=40 + k)
+            else:
+                lens = getattr(self.producer_function, "lengths", None)
+            if lens is None:
+                raise ValueError("variable_length windows need producer_function.lengths after post_init")
             engine.set_lengths(k, np.asarray(lens))
         engine.init_table(k, Pcg64(seed) if mode == "device" else None)
         if mode == "trace":

@@ -675,6 +675,7 @@ class DeviceEngine:
         self._table_targets = dev([[p + 4 * (N.FLAG_TABLE0 + k * N.FLAG_MAX_RANKS + self.me) for p in flag_pages]
                                    for k in range(self.P)])                     # [P, R]
         self._status_word()  # bounded waits report here
+        self.signal = torch.cuda.Stream(self.device, priority=-1)  # `free` tokens, see release_slot
         g = C.c_int32()
         N.check(N.lib().bddl_push_ctas_per_consumer(R, self.cfg.gather_max_ctas, C.byref(g)))
         d = N.PushDesc()
@@ -715,10 +716,18 @@ class DeviceEngine:
         group_in = {N.CVT_COPY: 16, N.CVT_U8_BF16: 8, N.CVT_F32_BF16: 32, N.CVT_U8_F32: 4, N.CVT_I32_I64: 8}
         return not s.var and s.sample_bytes % group_in[s.convert.mode] == 0
 
-    def release_slot(self, ring_slot: int, stream) -> None:
-        """Consumer side of the push form: tell every owner that `ring_slot` may be refilled."""
+    def release_slot(self, ring_slot: int, consumed_event) -> None:
+        """Consumer side of the push form: tell every owner that `ring_slot` may be refilled.
+
+        The signal runs on its own HIGH-priority stream behind the slot's `consumed` event, not on
+        the training stream.  Push kernels wait for this word from inside the kernel while they
+        occupy SMs, and the block dispatcher serves grids of one priority strictly in order: a
+        one-block signal kernel of normal priority can sit behind a partially dispatched push kernel
+        whose blocks wait for that very signal (measured: 3 fetch streams deadlocked this way).  A
+        higher-priority grid is dispatched first."""
+        stream_wait(self.signal, consumed_event)
         N.check(N.lib().bddl_flag_signal(C.c_void_p(self._free_targets[ring_slot].data_ptr()), self.n_instances,
-                                         self._use[ring_slot], 0, C.c_void_p(stream.cuda_stream)))
+                                         self._use[ring_slot], 0, C.c_void_p(self.signal.cuda_stream)))
         self.launches += 1
 
     # -- integrity mode -----------------------------------------------------------------------------------

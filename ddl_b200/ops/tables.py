@@ -56,7 +56,7 @@ _perm_scratch: dict = {}
 
 
 def perm_gen_scratch(device: torch.device, n: int, n_tables: int = 1) -> torch.Tensor:
-    """Device scratch for ``perm_gen`` (targets, reservation words, work lists: 20 bytes per entry),
+    """Device scratch for ``perm_gen`` (targets, reservation words, work lists: 28 bytes per entry),
     cached per device and grown on demand so the shuffle path never allocates in steady state."""
     need = n_tables * ((int(N.lib().bddl_perm_gen_scratch_bytes(n)) + 63) // 64 * 64)
     key = (device.type, device.index)

@@ -60,6 +60,9 @@ class StorageServer:
                               my_ary=window, n_instance=env.n_instances)
             dst = shard.tensor(torch.uint8, (s.nData, s.row_bytes))
             dst[:, :s.window_bytes].copy_(torch.from_numpy(window.reshape(s.nData, -1).view(np.uint8)))
+            if s.var:  # variable-size samples: the consumer needs the valid length of every row
+                lens = getattr(pf, "lengths", None)
+                comm.send_obj(None if lens is None else np.asarray(lens).astype(np.int32), i, tag=40 + k)
         if cuda:
             torch.cuda.synchronize(env.device)
         log.info("[%03d] storage rank holds %d shards for instances %s", me, len(work), hosted)

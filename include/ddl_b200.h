@@ -61,9 +61,9 @@ int bddl_partner_select(bddl_rng_state* s, int32_t n_instance, int32_t my_rank, 
 /* ---- N2: perm_gen (replaces the in-place row shuffle rng.shuffle(my_ary), invoked at
  *      ddl/datapusher.py:154).  Shuffles n_tables slot tables of n entries each (table t starts
  *      at d_tables + t*table_stride) with the RNG states d_states[t], which are advanced in
- *      place on the device.  Bit-exact with bddl_host_shuffle_u64.  One CTA of 512 threads per
- *      table: block-parallel draw generation and accept/reject, then the swaps applied in
- *      O(log n) rounds of deterministic reservations.  d_scratch: caller-owned device memory,
+ *      place on the device.  Bit-exact with bddl_host_shuffle_u64.  One thread-block cluster
+ *      (8 CTAs x 512 threads) per table: block-parallel draw generation and accept/reject, then
+ *      the swaps applied by the whole cluster in O(log n) rounds of deterministic reservations.  d_scratch: caller-owned device memory,
  *      n_tables * round_up(bddl_perm_gen_scratch_bytes(n), 64) bytes, 16-byte aligned. -------- */
 int64_t bddl_perm_gen_scratch_bytes(int64_t n);
 int bddl_perm_gen(uint64_t* d_tables, int64_t table_stride, int64_t n, bddl_rng_state* d_states,

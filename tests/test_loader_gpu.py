@@ -257,6 +257,19 @@ def test_multi_gpu_u8_to_bf16_with_integrity_mode(tmp_path, nproc, exchange):
 
 
 @pytest.mark.multigpu
+@pytest.mark.parametrize("exchange", ["pull", "push"])
+def test_two_gpus_variable_length_rows(tmp_path, exchange):
+    """Variable-size int32 rows (up to 2400 bytes) exchanged between two GPUs, widened to int64 and padded
+    while collating -- by the pull kernel and by the push kernel."""
+    _need_gpus(2)
+    cfg = {"n_instances": 2, "n_producers": 1, "n": 400, "v": 600, "B": 32, "epochs": 3, "fraction": 0.5,
+           "shuffle_mode": "device", "cpu": False, "ragged": True, "exchange": exchange, "timeout_s": 60.0,
+           "ring_depth": 3, "prefetch_depth": 2}
+    _torchrun(2, cfg, tmp_path)
+    _check_order(tmp_path, 2, 1, 400, 32, 3, 0.5)
+
+
+@pytest.mark.multigpu
 @pytest.mark.parametrize("nproc,multicast", [(2, "auto"), (2, "off"), (8, "auto")])
 def test_replicated_window_delivered_to_every_consumer(tmp_path, nproc, multicast):
     """replicate=True: every consumer receives instance 0's window.  Each sample is converted once by

@@ -117,3 +117,28 @@ def test_process_transport_declared_shuffle_double_windows(tmp_path):
     cfg = {"n_instances": 1, "n": 3000, "v": 9, "B": 512, "epochs": 7, "fraction": 0.5, "declare_seed": True}
     run_world(3, cfg, tmp_path)
     check(tmp_path, 1, 2, cfg)
+
+
+@pytest.mark.timeout(200)
+@pytest.mark.parametrize("declare", [False, True])
+def test_process_transport_resume_replays_to_the_checkpoint(tmp_path, declare):
+    """Checkpoint of the process transport: a fresh world (1 consumer + 2 producer processes) loaded with
+    a position continues with exactly the batches an uninterrupted run delivers from there on."""
+    n, B, E, e0, b0 = 1200, 100, 5, 2, 7
+    cfg = {"n_instances": 1, "n": n, "v": 4, "B": B, "epochs": E, "fraction": 0.0, "declare_seed": declare,
+           "resume": [e0, b0]}
+    run_world(3, cfg, tmp_path)
+    exp = expected_epochs(1, 2, n, B, E, 0.0)[0]
+    tail = np.concatenate([exp[e0][b0 * B:]] + [exp[e] for e in range(e0 + 1, E)])
+    assert np.array_equal(np.load(os.path.join(str(tmp_path), "seen_0.npy")), tail)
+
+
+@pytest.mark.timeout(200)
+@pytest.mark.parametrize("n_storage", [0, 1])
+def test_variable_length_windows_across_instances_and_storage_ranks(tmp_path, n_storage):
+    """Variable-size samples with the global exchange between two instances, with the shards on the
+    consumers' own ranks or on a dedicated storage rank (which then reports the row lengths)."""
+    cfg = {"n_instances": 2, "n_storage": n_storage, "n_producers": 1, "n": 200, "v": 24, "B": 16, "epochs": 3,
+           "fraction": 0.5, "shuffle_mode": "device", "ragged": True}
+    run_world(2 + n_storage, cfg, tmp_path)
+    check(tmp_path, 2, 1, cfg)

@@ -37,6 +37,30 @@ class ByteProducer(ddl.ProducerFunctionSkeleton):
         a[:, 4:] = ((gid[:, None] * 7 + np.arange(self.v - 4)[None, :]) % 251).astype(np.uint8)
 
 
+class RaggedProducer(ddl.ProducerFunctionSkeleton):
+    """Variable-size int32 rows: row of global id g holds g*100 + [0, len) and garbage beyond."""
+
+    def __init__(self, n, v):
+        super().__init__()
+        self.n, self.v = n, v
+
+    def on_init(self, **kw):
+        super().on_init(**kw)
+        from ddl_b200 import _native as N
+
+        cv = ddl.Convert(N.CVT_I32_I64, pad_value=-1)
+        return ddl.DataProducerOnInitReturn(self.n, self.v, (self.n, self.v), (self.v,), dtype=np.int32, convert=cv,
+                                            shuffle_seed=self.rank_global, variable_length=True)
+
+    def post_init(self, **kw):
+        a = kw["my_ary"]
+        self.lengths = np.random.default_rng(100 + self.rank_global).integers(1, self.v + 1, size=self.n)
+        gid = self.rank_global * 1_000_000 + np.arange(self.n)
+        a[...] = 77777
+        for i, l in enumerate(self.lengths):
+            a[i, :l] = gid[i] * 100 + np.arange(l)
+
+
 class IdProducer(ddl.ProducerFunctionSkeleton):
     def __init__(self, n, v, declare_seed, group_size):
         super().__init__()
@@ -71,6 +95,8 @@ def body(env, conn):
     n, v, B, E = CFG["n"], CFG["v"], CFG["B"], CFG["epochs"]
     group_size = env.n_producers + 1
     producer = ByteProducer(n, v) if CFG.get("u8") else IdProducer(n, v, CFG.get("declare_seed", False), group_size)
+    if CFG.get("ragged"):
+        producer = RaggedProducer(n, v)
     loader = ddl.DistributedDataLoader(producer, B, conn, E, CFG.get("fraction", 0.0), "sendrecv_replace", env.color,
                                        env.n_instances)
     seen = []
@@ -85,6 +111,35 @@ def body(env, conn):
                 fh.write(str(err))
             os._exit(0)
         os._exit(3)
+    if CFG.get("ragged"):
+        for e in range(E):
+            ids = []
+            for (x,) in loader:
+                lens = loader.batch_lengths().cpu().numpy()
+                x = x.cpu().numpy()
+                gid = x[:, 0] // 100
+                for j in range(B):
+                    want = np.random.default_rng(100 + int(gid[j]) // 1_000_000).integers(1, v + 1, size=n)[gid[j] % 1_000_000]
+                    assert lens[j] == want and np.array_equal(x[j, :want], gid[j] * 100 + np.arange(want))
+                    assert (x[j, want:] == -1).all(), "padding must replace whatever lies beyond the valid prefix"
+                ids.append(gid.astype(np.int64))
+                loader.mark(ddl.Marker.END_OF_BATCH)
+            loader.mark(ddl.Marker.END_OF_EPOCH)
+            seen.append(np.concatenate(ids))
+        np.save(os.path.join(CFG["out"], f"seen_{env.color}.npy"), np.stack(seen))
+        return
+    if CFG.get("resume"):
+        # a fresh world continues from a checkpointed position (process transport: replayed hand-overs)
+        e0, b0 = CFG["resume"]
+        loader.load_state_dict({"transport": "process", "epoch": e0, "batch": b0, "target_rank": 0})
+        ids = []
+        for e in range(e0, E):
+            for a, b in loader:
+                ids.append(a.detach().cpu().float().numpy()[:, 0].astype(np.int64))
+                loader.mark(ddl.Marker.END_OF_BATCH)
+            loader.mark(ddl.Marker.END_OF_EPOCH)
+        np.save(os.path.join(CFG["out"], f"seen_{env.color}.npy"), np.concatenate(ids))
+        return
     if CFG.get("u8"):
         pat = torch.arange(v - 4, device=env.device)[None, :]
         w = torch.tensor([1, 256, 65536, 16777216], device=env.device)
