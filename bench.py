@@ -164,7 +164,11 @@ def run_ours(args) -> dict:
                   "region lasts >= %.2f s and spans >= 2 window turnovers (index_exchange + perm_gen + "
                   "cross-rank barrier included)" % args.min_seconds,
         "exchange": {"remote_fraction": round(result["remote"], 4), "nvlink_in_gbs_per_gpu": round(nvl, 1),
-                     "frac_of_900_nominal": round(nvl / 900, 3), "frac_of_770_measured": round(nvl / 770, 3)},
+                     "frac_of_900_nominal": round(nvl / 900, 3), "frac_of_770_measured": round(nvl / 770, 3),
+                     # NVLink data counters of rank 0's GPU around the timed region next to the bytes the
+                     # slot tables ask for (prefetches in flight at either end included in the count)
+                     "nvlink_rx_bytes_counted": t.get("nvlink_rx_bytes"),
+                     "nvlink_rx_bytes_algorithmic": int(result["remote"] * args.batch * SAMPLE * t["total_steps"])},
         "roofline": {"hbm_gbs_per_gpu": round(hbm_gbs, 1), "hbm_peak_gbs": hbm_peak, "peak": how,
                      "frac_of_hbm_copy": round(hbm_gbs / hbm_peak, 3),
                      "bound": "HBM" if args.gpus == 1 else "NVLink (see exchange)"},

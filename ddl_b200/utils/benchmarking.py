@@ -131,16 +131,22 @@ def timed_loop(loader, env, steps, warmup, e2e: bool, min_seconds: float, min_to
     sampler = ClockSampler(dev.index or 0)
     if sample_clocks and cuda:
         sampler.start()
+    link0 = nvlink_counters(dev.index or 0) if (sample_clocks and cuda) else None
+    comm.barrier()
     l0 = N.launch_count()
     with Span() as sp:
         run(total)
     launches = N.launch_count() - l0
     comm.barrier()
+    link1 = nvlink_counters(dev.index or 0) if (sample_clocks and cuda) else None
+    comm.barrier()
     clocks = sampler.stop() if (sample_clocks and cuda) else None
     ms = max(sp.ms, sp.wall * 1e3) if e2e else sp.ms
     all_ms = comm.allgather_obj(ms)
     return {"ms": max(all_ms), "ms_min_rank": min(all_ms), "launches": launches, "clocks": clocks,
-            "repeats": repeats, "total_steps": total, "wall_s": sp.wall, "windows_crossed": total // max(1, bpw), "it": it}
+            "repeats": repeats, "total_steps": total, "wall_s": sp.wall, "windows_crossed": total // max(1, bpw), "it": it,
+            "nvlink_rx_bytes": (link1[1] - link0[1]) if (link0 and link1) else None,
+            "nvlink_tx_bytes": (link1[0] - link0[0]) if (link0 and link1) else None}
 
 
 def check_numerics(loader, it) -> dict:
@@ -159,3 +165,21 @@ def check_numerics(loader, it) -> dict:
     return {"rows": int(x.shape[0]), "mismatched_rows": bad_rows,
             "max_abs_err": float((x.double() - ref.double()).abs().max().item()),
             "finite": bool(torch.isfinite(x.float()).all().item()) if fl else True}
+
+
+def nvlink_counters(device_index: int):
+    """Sum of the NVLink data counters of one GPU, (tx_bytes, rx_bytes), from
+    ``nvidia-smi nvlink -gt d`` -- or None where the driver does not report them.  Bracketing a run
+    with two readings shows the traffic that really crossed the links next to the algorithmic bytes."""
+    import re
+
+    try:
+        out = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(device_index)], capture_output=True,
+                             text=True, timeout=20).stdout
+    except Exception:
+        return None
+    tx = [int(x) for x in re.findall(r"Data Tx:\s*(\d+)\s*KiB", out)]
+    rx = [int(x) for x in re.findall(r"Data Rx:\s*(\d+)\s*KiB", out)]
+    if not tx or not rx:
+        return None
+    return sum(tx) * 1024, sum(rx) * 1024
