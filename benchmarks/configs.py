@@ -26,13 +26,19 @@ CONFIGS = {
     "gpt2": (65536, 1024, np.int32, 512, lambda: ddl.Convert.widen_tokens(), (1024,)),
     "volume": (64, 4 * 128 ** 3, np.float32, 4, lambda: None, (4 * 128 ** 3,)),
     "volume_bf16": (64, 4 * 128 ** 3, np.float32, 4, lambda: ddl.Convert.cast_f32_bf16(), (4 * 128 ** 3,)),
+    # ImageNet-shaped uint8 -> bf16; with --replicate every consumer receives instance 0's window (push form:
+    # DDL_B200_EXCHANGE=push; DDL_B200_MULTICAST=auto|off selects multimem.st vs one store per consumer)
+    "imagenet": (4096, 3 * 224 * 224, np.uint8, 256,
+                 lambda: ddl.Convert.normalize_u8((0.485, 0.456, 0.406), (0.229, 0.224, 0.225), 224 * 224),
+                 (3 * 224 * 224,)),
 }
 
 
 class Synthetic(ddl.ProducerFunctionSkeleton):
-    def __init__(self, rows, nv, dtype, convert, splits):
+    def __init__(self, rows, nv, dtype, convert, splits, replicate=False):
         super().__init__()
         self.rows, self.nv, self.dtype, self.convert, self.splits = rows, nv, np.dtype(dtype).str, convert, splits
+        self.replicate = replicate
         self.rng = None
 
     def on_init(self, **kw):
@@ -40,7 +46,7 @@ class Synthetic(ddl.ProducerFunctionSkeleton):
         self.rng = np.random.default_rng(self.rank_global)
         return ddl.DataProducerOnInitReturn(self.rows, self.nv, (self.rows, self.nv), self.splits,
                                             dtype=np.dtype(self.dtype), convert=self.convert,
-                                            shuffle_seed=self.rank_global)
+                                            shuffle_seed=self.rank_global, replicate=self.replicate)
 
     def post_init(self, **kw):
         a = kw["my_ary"]
@@ -64,14 +70,18 @@ def main():
     ap.add_argument("--instances", default="world")
     ap.add_argument("--storage", type=int, default=0, help="dedicated storage GPUs (producers:consumers = storage:rest)")
     ap.add_argument("--out", default=None)
+    ap.add_argument("--replicate", action="store_true", help="replicated window: everybody receives instance 0's batches")
     ap.add_argument("--min-seconds", type=float, default=0.5)
     args = ap.parse_args()
     rows, nv, dtype, B, cvf, splits = CONFIGS[args.config]
     out = {}
+    eng_ref = []
+    loader_cfg = ddl.LoaderConfig.from_env(metrics=False, ring_depth=4, prefetch_depth=2, fetch_streams=2)
 
     def body(env, conn):
-        loader = ddl.DistributedDataLoader(Synthetic(rows, nv, dtype, cvf(), splits), B, conn, 10**9, 0.5,
+        loader = ddl.DistributedDataLoader(Synthetic(rows, nv, dtype, cvf(), splits, args.replicate), B, conn, 10**9, 0.5,
                                            "sendrecv_replace", env.color, env.n_instances)
+        eng_ref.append(loader.engine)
         t = timed_loop(loader, env, args.steps, args.warmup, False, args.min_seconds, int(2.5 * (rows // B)),
                        sample_clocks=env.comm_global.rank == 0)
         nums = env.comm_global.allgather_obj(check_numerics(loader, t.pop("it")))
@@ -84,6 +94,8 @@ def main():
                    out_dtype=str(x[0].dtype), ms_per_step=round(ms / steps, 5),
                    samples_per_s=round(n * B * steps / ms * 1e3, 1),
                    input_gbs=round(n * B * steps * sample_bytes / ms / 1e6, 1), rank=env.comm_global.rank,
+                   exchange=loader_cfg.exchange, replicate=args.replicate,
+                   multicast=bool(getattr(eng_ref[0], "mc_ring", 0)) if eng_ref else None,
                    steps=args.steps, repeats=t["repeats"], timed_region_s=round(ms * 1e-3, 4),
                    windows_crossed=t["windows_crossed"], clocks=t["clocks"],
                    mismatched_rows=sum(m["mismatched_rows"] for m in nums),
@@ -93,8 +105,7 @@ def main():
         loader.close()
 
     n_inst = args.instances if args.instances == "world" else int(args.instances)
-    cfg = ddl.LoaderConfig.from_env(metrics=False, ring_depth=4, prefetch_depth=2, fetch_streams=2)
-    ddl.distributed_dataloader(body, n_instances=n_inst, n_producers=None if n_inst != "world" else 1, config=cfg,
+    ddl.distributed_dataloader(body, n_instances=n_inst, n_producers=None if n_inst != "world" else 1, config=loader_cfg,
                                n_storage=args.storage)()
     if out.get("rank") == 0:
         out.pop("rank")
