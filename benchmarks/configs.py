@@ -70,13 +70,15 @@ def main():
     ap.add_argument("--instances", default="world")
     ap.add_argument("--storage", type=int, default=0, help="dedicated storage GPUs (producers:consumers = storage:rest)")
     ap.add_argument("--out", default=None)
+    ap.add_argument("--timeout-s", type=float, default=None)
     ap.add_argument("--replicate", action="store_true", help="replicated window: everybody receives instance 0's batches")
     ap.add_argument("--min-seconds", type=float, default=0.5)
     args = ap.parse_args()
     rows, nv, dtype, B, cvf, splits = CONFIGS[args.config]
     out = {}
     eng_ref = []
-    loader_cfg = ddl.LoaderConfig.from_env(metrics=False, ring_depth=4, prefetch_depth=2, fetch_streams=2)
+    loader_cfg = ddl.LoaderConfig.from_env(metrics=False, ring_depth=4, prefetch_depth=2, fetch_streams=2,
+                                           timeout_s=args.timeout_s)
 
     def body(env, conn):
         loader = ddl.DistributedDataLoader(Synthetic(rows, nv, dtype, cvf(), splits, args.replicate), B, conn, 10**9, 0.5,

@@ -321,6 +321,11 @@ class DevicePusher:
             before = eng.cur[k]
             execute_callbacks("global_shuffle", callbacks=self.callbacks, compat=self.compat)
             if eng.cur[k] == before:
+                if eng.push and eng.specs[k].replicate:
+                    # instance 0's table is read by every GPU for every consumer: nobody may rewrite a
+                    # table buffer before ALL ranks have finished the window that used it (the
+                    # exchange, when active, brings this barrier along)
+                    eng.stream_barrier()
                 eng.copy_forward(k)  # no exchange this iteration: still move to the other buffer
             if self.mode == "device":
                 eng.local_shuffle(k)

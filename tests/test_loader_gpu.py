@@ -161,7 +161,11 @@ def _torchrun(nproc, cfg, tmp_path, timeout=240):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(HERE, "workers", "run_loader.py")]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
-    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    if res.returncode != 0:
+        import glob
+
+        errs = "".join(f"--- {os.path.basename(f)}\n{open(f).read()[-1500:]}" for f in sorted(glob.glob(os.path.join(str(tmp_path), "error_rank*.txt")))[:2])
+        raise AssertionError(errs or (res.stdout[-3000:] + res.stderr[-3000:]))
 
 
 @pytest.mark.parametrize("declare", [False, True])

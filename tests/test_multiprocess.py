@@ -30,7 +30,11 @@ def run_world(nproc, cfg, tmp_path, timeout=150, extra_env=None):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), WORKER]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
-    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    if res.returncode != 0:
+        import glob
+
+        errs = "".join(f"--- {os.path.basename(f)}\n{open(f).read()[-1500:]}" for f in sorted(glob.glob(os.path.join(str(tmp_path), "error_rank*.txt")))[:2])
+        raise AssertionError(errs or (res.stdout[-3000:] + res.stderr[-3000:]))
     return res
 
 

@@ -198,4 +198,12 @@ if __name__ == "__main__":
     main = ddl.distributed_dataloader(body, n_instances=CFG["n_instances"], n_producers=CFG.get("n_producers"),
                                       config=cfg, device="cpu" if CFG.get("cpu", True) else None,
                                       n_storage=CFG.get("n_storage", 0))
-    main()
+    try:
+        main()
+    except BaseException:
+        import traceback
+
+        # torchrun buries a rank's traceback under its own report: keep a copy the test can show
+        with open(os.path.join(CFG["out"], f"error_rank{os.environ.get('RANK', '0')}.txt"), "w") as fh:
+            traceback.print_exc(file=fh)
+        raise
