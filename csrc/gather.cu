@@ -620,7 +620,8 @@ __global__ void __launch_bounds__(NW * 32) push_tma_cvt_kernel(const __grid_cons
         if (st) st |= (3u << 4) | ((uint32_t)q.me << 8);
     }
     if (st && threadIdx.x == 0) {
-        st_release_sys_u32(q.status, st);
+        // keep the FIRST failure: later launches only report "stopped"
+        if (ld_acquire_sys_u32(q.status) == 0) st_release_sys_u32(q.status, st | (blockIdx.x << 16));
         // a wait gave up: set this rank's stop word so that the launches already queued behind this
         // one return at once instead of timing out one after the other
         st_release_sys_u32(my_page + q.stop_word, 1u);
@@ -932,7 +933,12 @@ extern "C" int bddl_push_ctas_per_consumer(int32_t n_ranks, int32_t max_ctas, in
     int sms = 0;
     int rc = sm_count(&sms);
     if (rc) return rc;
-    const int cap = max_ctas > 0 ? max_ctas : sms;
+    // Push CTAs take a whole SM each (200 KB of shared memory) and may wait inside the kernel for a
+    // counter.  The small kernels that move those counters (free tokens, flag barrier, table
+    // production) must always find an SM, also when every push CTA of this GPU is waiting -- with a
+    // multicast launch all of them wait for the slowest consumer at once -- so eight SMs are never
+    // given to push CTAs.
+    const int cap = max_ctas > 0 ? max_ctas : (sms > 16 ? sms - 8 : sms);
     *out = cap / n_ranks > 0 ? cap / n_ranks : 1;
     return 0;
 }

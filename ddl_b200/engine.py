@@ -511,8 +511,10 @@ class DeviceEngine:
 
             code = int(self._status[0])
             what = {1: "timed out", 2: "was stopped"}.get(code & 15, "failed")
-            which = {0: "a peer's flag", 1: f"the `free` word of consumer {code >> 8}",
-                     2: f"the `table` word of consumer {code >> 8}", 3: "this rank's `ready` word"}.get((code >> 4) & 15)
+            peer = (code >> 8) & 255
+            which = {0: "a peer's flag", 1: f"the `free` word of consumer {peer}",
+                     2: f"the `table` word of consumer {peer}", 3: "this rank's `ready` word"}.get((code >> 4) & 15)
+            which += f" (block {code >> 16})"
             raise LoaderTimeoutError(f"a bounded device-side wait on {which} {what} (timeout_s={self.cfg.timeout_s}); "
                                      f"flag page: {self.flag_page_summary()}")
 
@@ -528,6 +530,7 @@ class DeviceEngine:
             return str({"ready": w[N.FLAG_READY0:N.FLAG_READY0 + D].tolist(),
                         "free": [w[N.FLAG_FREE0 + s * M:N.FLAG_FREE0 + s * M + R].tolist() for s in range(D)],
                         "done": [w[N.FLAG_DONE0 + s * M:N.FLAG_DONE0 + s * M + R].tolist() for s in range(D)],
+                        "done_mc": w[288:288 + D].tolist(), "rank": self.me,
                         "table": [w[N.FLAG_TABLE0 + k * M:N.FLAG_TABLE0 + k * M + R].tolist() for k in range(self.P)],
                         "use": getattr(self, "_use", None)})
         except Exception as e:  # diagnostics must never mask the timeout itself
