@@ -215,10 +215,19 @@ def _need_gpus(n):
         pytest.skip(f"needs {n} CUDA devices")
 
 
-def _check_order(tmp_path, n_inst, P, n, B, E, fraction):
+ID_STRIDE = 100_000  # float32 ids of the id/payload worker stay exact (< 2^24) for up to 160 producers
+
+
+def _restride(ids):
+    """Oracle ids (rank_global * 1e6 + row) in the worker's id_stride encoding."""
+    return ids // 1_000_000 * ID_STRIDE + ids % 1_000_000
+
+
+def _check_order(tmp_path, n_inst, P, n, B, E, fraction, restride=False):
     exp = expected_epochs(n_inst, P, n, B, E, fraction)
     for i in range(n_inst):
-        assert np.array_equal(np.load(os.path.join(str(tmp_path), f"seen_{i}.npy")), exp[i]), f"instance {i}"
+        want = _restride(exp[i]) if restride else exp[i]
+        assert np.array_equal(np.load(os.path.join(str(tmp_path), f"seen_{i}.npy")), want), f"instance {i}"
 
 
 @pytest.mark.multigpu
@@ -230,9 +239,9 @@ def test_multi_gpu_push_exchange(tmp_path, nproc):
     _need_gpus(nproc)
     cfg = {"n_instances": nproc, "n_producers": 2, "n": 4096, "v": 32, "B": 256, "epochs": 6, "fraction": 0.5,
            "shuffle_mode": "device", "declare_seed": True, "cpu": False, "exchange": "push", "timeout_s": 60.0,
-           "ring_depth": 4, "prefetch_depth": 2, "fetch_streams": 2}
+           "ring_depth": 4, "prefetch_depth": 2, "fetch_streams": 2, "id_stride": ID_STRIDE}
     _torchrun(nproc, cfg, tmp_path)
-    _check_order(tmp_path, nproc, 2, 4096, 256, 6, 0.5)
+    _check_order(tmp_path, nproc, 2, 4096, 256, 6, 0.5, restride=True)
 
 
 @pytest.mark.multigpu
@@ -242,9 +251,10 @@ def test_multi_gpu_global_shuffle_over_nvlink(tmp_path, nproc, barrier):
     """One process per GPU: slot tables exchanged and samples pulled through peer mappings."""
     _need_gpus(nproc)
     cfg = {"n_instances": nproc, "n_producers": 2, "n": 4096, "v": 32, "B": 256, "epochs": 6, "fraction": 0.5,
-           "shuffle_mode": "device", "declare_seed": True, "cpu": False, "barrier": barrier, "timeout_s": 60.0}
+           "shuffle_mode": "device", "declare_seed": True, "cpu": False, "barrier": barrier, "timeout_s": 60.0,
+           "id_stride": ID_STRIDE}
     _torchrun(nproc, cfg, tmp_path)
-    _check_order(tmp_path, nproc, 2, 4096, 256, 6, 0.5)
+    _check_order(tmp_path, nproc, 2, 4096, 256, 6, 0.5, restride=True)
 
 
 @pytest.mark.multigpu
@@ -283,9 +293,10 @@ def test_replicated_window_delivered_to_every_consumer(tmp_path, nproc, multicas
     _need_gpus(nproc)
     cfg = {"n_instances": nproc, "n_producers": 2, "n": 4096, "v": 32, "B": 256, "epochs": 6, "fraction": 0.5,
            "shuffle_mode": "device", "declare_seed": True, "cpu": False, "exchange": "push", "timeout_s": 60.0,
-           "ring_depth": 4, "prefetch_depth": 2, "fetch_streams": 2, "replicate": True, "multicast": multicast}
+           "ring_depth": 4, "prefetch_depth": 2, "fetch_streams": 2, "replicate": True, "multicast": multicast,
+           "id_stride": ID_STRIDE}
     _torchrun(nproc, cfg, tmp_path)
-    exp = expected_epochs(nproc, 2, 4096, 256, 6, 0.5)[0]
+    exp = _restride(expected_epochs(nproc, 2, 4096, 256, 6, 0.5)[0])
     for i in range(nproc):
         assert np.array_equal(np.load(os.path.join(str(tmp_path), f"seen_{i}.npy")), exp), f"consumer {i}"
 

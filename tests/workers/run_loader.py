@@ -77,7 +77,8 @@ class IdProducer(ddl.ProducerFunctionSkeleton):
 
     def post_init(self, **kw):
         self.my_ary = kw["my_ary"]
-        gid = (0 if CFG.get("small_ids") else self.rank_global * 1_000_000) + np.arange(self.n)
+        # ids travel as float32: they must stay below 2^24, so worlds with many producers use a smaller stride
+        gid = (0 if CFG.get("small_ids") else self.rank_global * CFG.get("id_stride", 1_000_000)) + np.arange(self.n)
         self.my_ary[:, 0] = gid.astype(np.float32)
         self.my_ary[:, 1:] = (gid[:, None] % 97).astype(np.float32)
 
