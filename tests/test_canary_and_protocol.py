@@ -166,3 +166,32 @@ LoaderMachine.TestCase.settings = settings(max_examples=12, stateful_step_count=
                                             suppress_health_check=list(HealthCheck),
                                             phases=(Phase.explicit, Phase.reuse, Phase.generate))
 TestLoaderMachine = LoaderMachine.TestCase
+
+
+def test_reference_batch_matches_delivered_batch_on_the_cpu_engine():
+    """`loader.reference_batch()` (independent row fetch + plain PyTorch convert) equals what the loader
+    delivered, bit for bit -- the oracle the multi-GPU benchmarks use, exercised here on the CPU engine with a
+    converting window (uint8 -> bf16, per-channel scale and bias)."""
+    n, B, hw = 256, 32, 48
+    cv = ddl.Convert.normalize_u8((0.485, 0.456, 0.406), (0.229, 0.224, 0.225), hw)
+    data = np.random.default_rng(4).integers(0, 256, size=(n, 3 * hw), dtype=np.uint8)
+
+    class Img(ddl.ProducerFunctionSkeleton):
+        def on_init(self, **kw):
+            super().on_init(**kw)
+            return ddl.DataProducerOnInitReturn(n, 3 * hw, (n, 3 * hw), (3 * hw,), dtype=np.uint8, convert=cv,
+                                                shuffle_seed=9)
+
+        def post_init(self, **kw):
+            kw["my_ary"][...] = data
+
+    from ddl_b200.connection import Connection
+    from ddl_b200.parallel.topology import init_env
+
+    env = init_env(1, n_producers=1, device=torch.device("cpu"))
+    loader = ddl.DistributedDataLoader(Img(), B, Connection(env.comm_per_gpu_shm, env, ddl.LoaderConfig(metrics=False)), 1)
+    for (x,) in loader:
+        (ref,) = loader.reference_batch()
+        assert x.dtype == torch.bfloat16 and torch.equal(x.view(torch.int16), ref.view(torch.int16))
+        loader.mark(ddl.Marker.END_OF_BATCH)
+    loader.mark(ddl.Marker.END_OF_EPOCH)

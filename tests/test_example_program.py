@@ -31,3 +31,13 @@ def test_program_single_process():
     res = subprocess.run([sys.executable, SCRIPT], env=env, capture_output=True, text=True, timeout=95)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
     assert "Training finished" in res.stdout
+
+
+@pytest.mark.timeout(150)
+def test_training_and_validation_example_single_process():
+    """Two windows per instance, one of them replicated (examples/train_with_validation.py), on the CPU path."""
+    env = dict(os.environ, OMP_NUM_THREADS="2", CUDA_VISIBLE_DEVICES="")
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "examples", "train_with_validation.py")], env=env,
+                         capture_output=True, text=True, timeout=140)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    assert "epoch 5 (validate): 16 batches" in res.stdout
