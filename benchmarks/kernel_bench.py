@@ -70,6 +70,48 @@ def bench_gather(name, convert, sample_bytes, batch, shard_bytes, variant, tune,
     }
 
 
+def bench_gather_overlapped(name, convert, sample_bytes, batch, shard_bytes, variant, tune, streams=3, iters=60,
+                            warmup=6):
+    """The deployed shape of the loader: `streams` launches in flight on as many streams (ring of output buffers),
+    timed as a whole between two events on the default stream -- ramp and tail of one launch hide behind the next."""
+    dev = torch.device("cuda:0")
+    row_bytes = round_up(sample_bytes, 16)
+    rows = max(batch * 4, shard_bytes // row_bytes)
+    shard = torch.randint(0, 255, (rows * row_bytes,), dtype=torch.uint8, device=dev)
+    plan = GatherPlan(SourceTable([shard.data_ptr()], dev), row_bytes, sample_bytes, convert, variant=variant, tune=tune)
+    n_lists = iters + warmup
+    perm = torch.randperm(rows, device=dev)
+    perm = perm.repeat((n_lists * batch + perm.numel() - 1) // perm.numel())[: n_lists * batch]
+    slots = perm.to(torch.int64).contiguous().view(n_lists, batch)
+    n_out = 2 * streams
+    outs = [plan.alloc_batch(batch) for _ in range(n_out)]
+    ss = [torch.cuda.Stream(dev) for _ in range(streams)]
+    main = torch.cuda.current_stream(dev)
+
+    def run(first, count):
+        for i in range(first, first + count):
+            plan.run(slots[i], outs[i % n_out], stream=ss[i % streams])
+
+    run(0, warmup)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(main)
+    for st in ss:
+        st.wait_event(a)
+    run(warmup, iters)
+    for st in ss:
+        main.wait_stream(st)
+    b.record(main)
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / iters
+    hbm, how = peaks()
+    gbs = batch * (sample_bytes + plan.out_sample_bytes) / ms / 1e6
+    return {"kernel": "exchange_gather_collate", "case": name, "variant": ["auto", "ldg", "tma"][variant], "tune": tune,
+            "streams": streams, "batch": batch, "sample_bytes": sample_bytes, "ms_per_launch": round(ms, 4),
+            "samples_per_s": round(batch / ms * 1e3), "gbs_in_plus_out": round(gbs, 1),
+            "frac_of_hbm_copy": round(gbs / hbm, 3), "peak": how}
+
+
 def bench_perm(n, tables=1, iters=5):
     dev = torch.device("cuda:0")
     t = torch.arange(n, dtype=torch.int64, device=dev).repeat(tables, 1).contiguous()
@@ -129,6 +171,12 @@ def main():
             r = bench_gather("imagenet_copy_batch_sweep", Convert.copy(), 150528, b, 4 << 30, N.VARIANT_TMA, 0)
             results.append(r)
             print(json.dumps(r), flush=True)
+    if not args.only or "overlap" in args.only:
+        for b in (64, 256, 1024):
+            for streams in (1, 3):
+                r = bench_gather_overlapped("imagenet_u8_bf16_overlap", img, 150528, b, 4 << 30, N.VARIANT_TMA, 0, streams)
+                results.append(r)
+                print(json.dumps(r), flush=True)
     if not args.only or "sm_budget" in args.only:
         for ctas in (8, 16, 32, 64):
             r = bench_gather("imagenet_u8_bf16_sm_budget", img, 150528, 256, 2 << 30, N.VARIANT_TMA, 0, max_ctas=ctas)
