@@ -30,6 +30,7 @@ import torch
 
 from . import _native as N
 from .config import LoaderConfig
+from .exceptions import ShutdownError
 from .connection import Connection
 from .datapusher import DevicePusher
 from .datasetwrapper import ProducerFunctionSkeleton
@@ -239,6 +240,8 @@ class DistributedDataLoader(DistributedDataloaderABC):
             raise IndexError
         if idx < 0:
             raise ValueError
+        if self._finalized:
+            raise ShutdownError("the loader was closed (all epochs consumed, or close() was called)")
         k = self.target_rank - 1
         b = idx % self.batches_per_window[k]
         if self.transport == "process" and not self.cuda:

@@ -13,7 +13,7 @@ class DoesNotMatchError(Exception):
 
 
 class ShutdownError(RuntimeError):
-    """A wait was cancelled because the loader is shutting down."""
+    """The loader was used after it shut down (all epochs consumed, or ``close()`` was called)."""
 
 
 class LoaderTimeoutError(TimeoutError):

@@ -93,3 +93,30 @@ def test_metrics_count_batches_and_bytes():
         assert m["batches"] >= 4 and m["samples"] >= 64 and m["bytes_in"] >= 64 * 16
 
     _with_loader(body)
+
+
+def test_batches_after_shutdown_raise():
+    """A closed loader says so instead of touching released buffers."""
+    import numpy as np
+    import pytest
+    import torch
+
+    import ddl_b200 as ddl
+    from ddl_b200.connection import Connection
+    from ddl_b200.exceptions import ShutdownError
+    from ddl_b200.parallel.topology import init_env
+
+    class P(ddl.ProducerFunctionSkeleton):
+        def on_init(self, **kw):
+            super().on_init(**kw)
+            return ddl.DataProducerOnInitReturn(64, 4, (64, 4), (4,), shuffle_seed=1)
+
+        def post_init(self, **kw):
+            kw["my_ary"][...] = np.arange(256, dtype=np.float32).reshape(64, 4)
+
+    env = init_env(1, n_producers=1, device=torch.device("cpu"))
+    loader = ddl.DistributedDataLoader(P(), 16, Connection(env.comm_per_gpu_shm, env, ddl.LoaderConfig(metrics=False)), 1)
+    _ = loader[0]
+    loader.close()
+    with pytest.raises(ShutdownError):
+        loader[0]
