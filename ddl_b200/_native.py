@@ -79,6 +79,7 @@ class GatherDesc(C.Structure):
 # flag page layout of the device transport (mirror of the BDDL_FLAG_* constants)
 FLAG_PAGE_BYTES, FLAG_MAX_RANKS, FLAG_MAX_SLOTS, FLAG_MAX_WINDOWS = 16384, 64, 16, 24
 FLAG_BARRIER0, FLAG_READY0, FLAG_STOP, FLAG_FREE0, FLAG_DONE0, FLAG_TABLE0 = 0, 256, 272, 512, 1536, 2560
+FLAG_DONE_MC0 = 288
 
 
 class PushDesc(C.Structure):

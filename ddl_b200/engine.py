@@ -345,13 +345,11 @@ class DeviceEngine:
             try:
                 return self.heap.alloc_vmm("ring", nbytes, multicast=True)
             except N.NativeError as e:
-                ok = False
+                # a box without VMM support raises before any collective step of alloc_vmm, on every
+                # rank alike (the capability query is the same on one box): all ranks fall back together
                 if self.cfg.multicast == "on":
                     raise
                 log.info("VMM ring unavailable (%s); using a cudaMalloc ring", e)
-            # a rank without VMM support raises before any collective step of alloc_vmm: all ranks
-            # take the same branch because the capability query is the same on one box
-            del ok
         if self.cfg.multicast == "on" and self.cfg.exchange == "push" and self.n_instances > 1:
             raise RuntimeError("multicast='on' needs CUDA devices with VMM and NVLS multicast support")
         return self.heap.alloc("ring", nbytes, zero=False)
@@ -530,7 +528,7 @@ class DeviceEngine:
             return str({"ready": w[N.FLAG_READY0:N.FLAG_READY0 + D].tolist(),
                         "free": [w[N.FLAG_FREE0 + s * M:N.FLAG_FREE0 + s * M + R].tolist() for s in range(D)],
                         "done": [w[N.FLAG_DONE0 + s * M:N.FLAG_DONE0 + s * M + R].tolist() for s in range(D)],
-                        "done_mc": w[288:288 + D].tolist(), "rank": self.me,
+                        "done_mc": w[N.FLAG_DONE_MC0:N.FLAG_DONE_MC0 + D].tolist(), "rank": self.me,
                         "table": [w[N.FLAG_TABLE0 + k * M:N.FLAG_TABLE0 + k * M + R].tolist() for k in range(self.P)],
                         "use": getattr(self, "_use", None)})
         except Exception as e:  # diagnostics must never mask the timeout itself
