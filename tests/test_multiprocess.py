@@ -146,3 +146,17 @@ def test_variable_length_windows_across_instances_and_storage_ranks(tmp_path, n_
            "fraction": 0.5, "shuffle_mode": "device", "ragged": True}
     run_world(2 + n_storage, cfg, tmp_path)
     check(tmp_path, 2, 1, cfg)
+
+
+@pytest.mark.timeout(300)
+def test_device_transport_eight_instances_two_producers(tmp_path):
+    """8 instances x 2 producers on the CPU engine: partner tables with several cycles (n=8), two
+    windows rotating, the order of every consumer equal to the reference semantics.  Ids use a smaller stride so
+    that 24 producers' float32 ids stay exact."""
+    cfg = {"n_instances": 8, "n_producers": 2, "n": 640, "v": 6, "B": 64, "epochs": 6, "fraction": 0.5,
+           "shuffle_mode": "device", "declare_seed": True, "id_stride": 100_000}
+    run_world(8, cfg, tmp_path, timeout=280)
+    exp = expected_epochs(8, 2, 640, 64, 6, 0.5)
+    for i in range(8):
+        want = exp[i] // 1_000_000 * 100_000 + exp[i] % 1_000_000
+        assert np.array_equal(np.load(os.path.join(str(tmp_path), f"seen_{i}.npy")), want), f"instance {i}"
